@@ -1,0 +1,163 @@
+/* b2c — B200-native gradient synchronisation: C-ABI boundary.
+ *
+ * This header is the drop-in boundary for the ONE data-parallel hot path of
+ * ray_lightning (per-step gradient allreduce + initial parameter broadcast).
+ * The reference owns no native code: each entry point below replaces a
+ * *library call* the reference reaches through torch c10d / Horovod.  Citations
+ * are `path:line` into the reference tree (ray_lightning/...) or, where the
+ * arithmetic lives upstream, `torch:<file>:<line>` into the installed torch
+ * 2.11 (see SURVEY.md §2a for the call-site inventory C1..C9).
+ *
+ * Conventions
+ *   - plain C, no torch / C++ types; loadable with ctypes / cgo / JNI.
+ *   - return 0 on success, negative B2C_E* library code, or a positive
+ *     cudaError_t.  Never throws, never exits.  b2c_last_error() returns a
+ *     thread-local human-readable string for the last failing call.
+ *   - data calls (allreduce / broadcast / barrier) only ENQUEUE on the given
+ *     stream; no host synchronisation.  create / import / destroy are
+ *     synchronous and must be called by every rank of the group.
+ *   - all ranks of a comm must issue the same sequence of data calls with the
+ *     same sizes and parameters (the cross-GPU epoch counter is implicit).
+ *   - the caller owns `buf` and keeps it alive until the stream passes the op;
+ *     the library owns arena, flags and peer mappings.
+ *   - calls on one comm must be stream-ordered (one stream at a time).
+ */
+#ifndef B2C_H_
+#define B2C_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2C_VERSION 100          /* 0.1.0 */
+#define B2C_MAX_WORLD 8          /* one NVSwitch domain */
+#define B2C_MAX_BLOCKS 128       /* independent flag channels per comm */
+#define B2C_EXPORT_BLOB_BYTES 256
+
+typedef struct b2c_comm b2c_comm;
+typedef void* b2c_stream_t;      /* a cudaStream_t; NULL = legacy default stream */
+
+/* element types (dtype = what lives in the caller's buffer,
+ * wire_dtype = what crosses NVLink / sits in the arena) */
+enum { B2C_F32 = 0, B2C_BF16 = 1, B2C_U8 = 2 };
+
+/* algorithm selector for b2c_allreduce */
+enum {
+  B2C_ALGO_AUTO = 0,          /* one-shot below the crossover, two-shot above */
+  B2C_ALGO_ONESHOT = 1,       /* every rank pulls all W copies and reduces locally */
+  B2C_ALGO_TWOSHOT = 2,       /* reduce-scatter then all-gather (variant by param) */
+};
+
+/* keys for b2c_set_param / b2c_get_param */
+enum {
+  B2C_PARAM_CROSSOVER_BYTES = 0,  /* AUTO: wire bytes above which two-shot is used */
+  B2C_PARAM_MAX_BLOCKS_ONESHOT = 1,
+  B2C_PARAM_MAX_BLOCKS_TWOSHOT = 2,
+  B2C_PARAM_THREADS = 3,          /* threads per CTA: 128..1024, multiple of 32 */
+  B2C_PARAM_TIMEOUT_MS = 4,       /* bounded spin in the cross-GPU barrier */
+  B2C_PARAM_TWOSHOT_VARIANT = 5,  /* 0 = pull-reduce + push (default), 1 = pull + pull */
+  B2C_PARAM_MAX_BLOCKS_BCAST = 6,
+  B2C_PARAM__COUNT = 7
+};
+
+/* error codes */
+enum {
+  B2C_OK = 0,
+  B2C_EINVAL = -1,     /* bad argument */
+  B2C_ESTATE = -2,     /* call not valid in this state (e.g. data call before import) */
+  B2C_ETOOBIG = -3,    /* request exceeds a stated capacity */
+  B2C_ETIMEOUT = -4,   /* a peer did not arrive at the flag barrier in time (sticky) */
+  B2C_ENOPEER = -5,    /* peer memory cannot be mapped (no P2P path / different node) */
+  B2C_EUNSUPPORTED = -6
+};
+
+typedef struct b2c_stats {
+  uint64_t calls_allreduce;
+  uint64_t calls_broadcast;
+  uint64_t calls_barrier;
+  uint64_t launches;            /* kernels launched by this comm */
+  uint64_t bytes_allreduce;     /* user bytes reduced */
+  uint64_t bytes_broadcast;
+  uint64_t oneshot_launches;
+  uint64_t twoshot_launches;
+  uint32_t last_algo;           /* B2C_ALGO_* actually used by the last allreduce */
+  uint32_t last_blocks;         /* grid.x of the last launch */
+  uint32_t last_threads;
+  uint32_t device_status;       /* 0, or the sticky error code the kernels reported */
+  uint32_t device_status_detail[3]; /* epoch, block, peer at failure */
+  uint32_t reserved;
+} b2c_stats;
+
+/* ---- library ---------------------------------------------------------- */
+
+int b2c_version(void);
+const char* b2c_last_error(void);
+
+/* ---- communicator life cycle -------------------------------------------
+ * Replaces the NCCL communicator that torch builds lazily behind
+ * ray_lightning/ray_ddp.py:232-237 (init_process_group("nccl")) for the
+ * gradient path only; the torch process group stays for control collectives.
+ *
+ * b2c_comm_create: cudaMalloc one symmetric region on `device`
+ *   (flag page + 2 arena slots, `arena_bytes` total for the two slots).
+ * b2c_comm_export: fill `blob` (B2C_EXPORT_BLOB_BYTES) with the CUDA IPC handle,
+ *   GPU UUID, pid and geometry; `*len` is in/out.
+ * b2c_comm_import: `blobs` = world blobs concatenated in rank order (own blob
+ *   included); maps every peer with cudaIpcOpenMemHandle (or direct peer access
+ *   when the peer lives in this process).  After import the comm is ready.
+ * b2c_comm_destroy: closes peer mappings and frees the region.  Replaces what
+ *   ray_ddp.py:109-121 (teardown) has to do before the actors are killed. */
+int b2c_comm_create(int rank, int world, int device, size_t arena_bytes, b2c_comm** out);
+int b2c_comm_export(b2c_comm* comm, void* blob, size_t* len);
+int b2c_comm_import(b2c_comm* comm, const void* blobs, size_t len_each);
+int b2c_comm_destroy(b2c_comm* comm);
+
+/* Single-device group: `world` virtual ranks on ONE GPU, peers addressed
+ * directly, every data call is ONE cooperative launch that runs all ranks'
+ * CTAs side by side (grid.y = world).  Used to exercise the complete
+ * cross-rank protocol (flags, epochs, double buffering) on a one-GPU box and
+ * for the HBM-bound roofline at N=1.  No reference counterpart. */
+int b2c_group_create_local(int world, int device, size_t arena_bytes, b2c_comm** out_comms);
+int b2c_group_destroy_local(b2c_comm** comms, int world);
+
+/* ---- data path ---------------------------------------------------------
+ * b2c_allreduce: in place, buf[i] = (sum over ranks r=0..W-1, in rank order,
+ *   fp32 accumulate) * scale, rounded once to `dtype`.
+ *   Replaces C3 — the per-bucket allreduce the c10d Reducer issues behind
+ *   ray_ddp.py:218-219 (torch:distributed/algorithms/ddp_comm_hooks/
+ *   default_hooks.py:18-32, div by W then all_reduce SUM) — and C6, Horovod's
+ *   allreduce_async_(op=Average) behind ray_horovod.py:159.
+ *   (dtype, wire_dtype) in {(F32,F32), (BF16,BF16), (F32,BF16)}; the last is the
+ *   bf16_compress_hook analogue (default_hooks.py:57-93): cast fused into the
+ *   staging pass, result is bf16-representable and written back as fp32.
+ * b2c_broadcast: bit-exact copy of root's `bytes` to every rank.  Replaces C2
+ *   (_sync_module_states, torch:distributed/utils.py:289-328, reached from the
+ *   DDP constructor behind ray_ddp.py:218-219), C4 (_sync_buffers) and C5
+ *   (hvd.broadcast_parameters behind ray_horovod.py:158).
+ * b2c_barrier: cross-GPU flag barrier on the stream.  Replaces C7 (hvd.join). */
+int b2c_allreduce(b2c_comm* comm, void* buf, size_t count, int dtype, int wire_dtype,
+                  float scale, int algo, b2c_stream_t stream);
+int b2c_broadcast(b2c_comm* comm, void* buf, size_t bytes, int root, b2c_stream_t stream);
+int b2c_barrier(b2c_comm* comm, b2c_stream_t stream);
+
+/* the same three on a local (single-device) group: bufs[r] is rank r's buffer */
+int b2c_group_allreduce(b2c_comm** comms, void** bufs, size_t count, int dtype, int wire_dtype,
+                        float scale, int algo, b2c_stream_t stream);
+int b2c_group_broadcast(b2c_comm** comms, void** bufs, size_t bytes, int root, b2c_stream_t stream);
+int b2c_group_barrier(b2c_comm** comms, b2c_stream_t stream);
+
+/* ---- knobs, counters, introspection ------------------------------------ */
+int b2c_set_param(b2c_comm* comm, int key, long value);
+int b2c_get_param(b2c_comm* comm, int key, long* value);
+int b2c_get_stats(b2c_comm* comm, b2c_stats* out);
+/* base address / size of one arena slot (device pointer, local rank) */
+int b2c_comm_arena(b2c_comm* comm, void** base, size_t* slot_bytes);
+int b2c_comm_info(b2c_comm* comm, int* rank, int* world, int* device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2C_H_ */

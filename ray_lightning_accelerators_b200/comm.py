@@ -1,0 +1,219 @@
+"""Python handles over the b2c C-ABI: ``Comm`` (one rank per process, peers mapped
+with CUDA IPC) and ``LocalGroup`` (W virtual ranks on one GPU, one cooperative
+launch per collective).
+
+PyTorch is used here for device memory and streams only; every byte of the data
+path moves inside libb2c.so's sm_100a kernels.
+"""
+import ctypes
+import os
+
+import torch
+
+from . import _lib
+from ._lib import (ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, BF16, F32, U8, B2cError)  # noqa: F401
+
+_DTYPES = {torch.float32: F32, torch.bfloat16: BF16}
+_ELEM = {F32: 4, BF16: 2}
+
+DEFAULT_ARENA_BYTES = int(os.environ.get("B2C_ARENA_BYTES", 256 << 20))
+
+# env knobs (the accelerator constructor signatures are frozen)
+_ENV_PARAMS = {
+    "B2C_CROSSOVER_BYTES": _lib.PARAM_CROSSOVER_BYTES,
+    "B2C_MAX_BLOCKS_ONESHOT": _lib.PARAM_MAX_BLOCKS_ONESHOT,
+    "B2C_MAX_BLOCKS_TWOSHOT": _lib.PARAM_MAX_BLOCKS_TWOSHOT,
+    "B2C_MAX_BLOCKS_BCAST": _lib.PARAM_MAX_BLOCKS_BCAST,
+    "B2C_THREADS": _lib.PARAM_THREADS,
+    "B2C_TIMEOUT_MS": _lib.PARAM_TIMEOUT_MS,
+    "B2C_TWOSHOT_VARIANT": _lib.PARAM_TWOSHOT_VARIANT,
+}
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        stream = torch.cuda.current_stream()
+    return ctypes.c_void_p(stream.cuda_stream)
+
+
+def _wire(t, wire_dtype):
+    d = _DTYPES.get(t.dtype)
+    if d is None:
+        raise TypeError(f"b2c allreduce supports float32 / bfloat16 tensors, got {t.dtype}")
+    if wire_dtype is None:
+        return d, d
+    w = _DTYPES.get(wire_dtype)
+    if w is None:
+        raise TypeError(f"unsupported wire dtype {wire_dtype}")
+    return d, w
+
+
+def _check_tensor(t):
+    if not t.is_cuda:
+        raise ValueError("b2c operates on CUDA tensors only (there is no CPU path)")
+    if not t.is_contiguous():
+        raise ValueError("b2c needs a contiguous tensor (DDP buckets are flat 1-D)")
+
+
+class _Base:
+    def _apply_env(self):
+        for env, key in _ENV_PARAMS.items():
+            if env in os.environ:
+                self.set_param(key, int(os.environ[env]))
+
+    def set_param(self, key, value):
+        _lib.check(self._lib.b2c_set_param(self._first, key, int(value)))
+
+    def get_param(self, key):
+        v = ctypes.c_long()
+        _lib.check(self._lib.b2c_get_param(self._first, key, ctypes.byref(v)))
+        return v.value
+
+    def stats(self):
+        s = _lib.Stats()
+        _lib.check(self._lib.b2c_get_stats(self._first, ctypes.byref(s)))
+        return s.as_dict()
+
+    def check_alive(self):
+        """Raise if a kernel reported a flag-barrier timeout (sticky)."""
+        st = self.stats()
+        if st["device_status"]:
+            raise B2cError(-int(st["device_status"]),
+                           "flag barrier timed out (epoch {}, channel {}, waiting for rank {})".format(
+                               *st["device_status_detail"]))
+
+
+class Comm(_Base):
+    """One rank of a cross-process group.  ``exchange`` is any callable that turns this
+    rank's blob (bytes) into the list of all ranks' blobs in rank order — the Ray object
+    store in the reference's world, a torch.distributed store / all_gather_object here."""
+
+    def __init__(self, rank, world, device=None, arena_bytes=None, exchange=None):
+        self._lib = _lib.load()
+        if device is None:
+            device = torch.cuda.current_device()
+        self.rank, self.world, self.device = int(rank), int(world), int(device)
+        self.arena_bytes = int(arena_bytes or DEFAULT_ARENA_BYTES)
+        h = ctypes.c_void_p()
+        _lib.check(self._lib.b2c_comm_create(self.rank, self.world, self.device, self.arena_bytes, ctypes.byref(h)))
+        self._h = h
+        self._first = h
+        self._apply_env()
+        if self.world > 1:
+            if exchange is None:
+                raise ValueError("world > 1 needs an `exchange` callable to swap IPC handles")
+            blobs = exchange(self.export())
+            self.import_(blobs)
+
+    @classmethod
+    def from_process_group(cls, group=None, device=None, arena_bytes=None):
+        """Bootstrap over an initialised torch.distributed group (control plane only:
+        W x 256 bytes, once).  ray_lightning/ray_ddp.py:232-237 creates that group."""
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+
+        def exchange(blob):
+            out = [None] * world
+            dist.all_gather_object(out, blob, group=group)
+            return out
+
+        return cls(rank, world, device=device, arena_bytes=arena_bytes, exchange=exchange)
+
+    def export(self):
+        buf = ctypes.create_string_buffer(_lib.EXPORT_BLOB_BYTES)
+        n = ctypes.c_size_t(_lib.EXPORT_BLOB_BYTES)
+        _lib.check(self._lib.b2c_comm_export(self._h, buf, ctypes.byref(n)))
+        return buf.raw[:n.value]
+
+    def import_(self, blobs):
+        if len(blobs) != self.world:
+            raise ValueError(f"need {self.world} blobs in rank order, got {len(blobs)}")
+        joined = b"".join(bytes(b) for b in blobs)
+        _lib.check(self._lib.b2c_comm_import(self._h, joined, len(joined) // self.world))
+
+    def allreduce(self, t, scale=None, wire_dtype=None, algo=ALGO_AUTO, stream=None):
+        """In place: t = sum_r t_r * scale (default 1/world), fp32 accumulate in rank order."""
+        _check_tensor(t)
+        d, w = _wire(t, wire_dtype)
+        if scale is None:
+            scale = 1.0 / self.world
+        _lib.check(self._lib.b2c_allreduce(self._h, ctypes.c_void_p(t.data_ptr()), t.numel(), d, w,
+                                           ctypes.c_float(scale), algo, _stream_ptr(stream)))
+        return t
+
+    def broadcast(self, t, root=0, stream=None):
+        _check_tensor(t)
+        _lib.check(self._lib.b2c_broadcast(self._h, ctypes.c_void_p(t.data_ptr()), t.numel() * t.element_size(),
+                                           int(root), _stream_ptr(stream)))
+        return t
+
+    def barrier(self, stream=None):
+        _lib.check(self._lib.b2c_barrier(self._h, _stream_ptr(stream)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            h, self._h = self._h, None
+            _lib.check(self._lib.b2c_comm_destroy(h))
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class LocalGroup(_Base):
+    """W virtual ranks on one GPU.  Same kernels, same flag protocol, one cooperative
+    launch per collective (grid.y = W) so the ranks' CTAs are guaranteed co-resident."""
+
+    def __init__(self, world, device=None, arena_bytes=None):
+        self._lib = _lib.load()
+        if device is None:
+            device = torch.cuda.current_device()
+        self.world, self.device = int(world), int(device)
+        self.arena_bytes = int(arena_bytes or DEFAULT_ARENA_BYTES)
+        self._arr = (ctypes.c_void_p * self.world)()
+        _lib.check(self._lib.b2c_group_create_local(self.world, self.device, self.arena_bytes, self._arr))
+        self._first = ctypes.c_void_p(self._arr[0])
+        self._open = True
+        self._apply_env()
+
+    def _ptrs(self, tensors):
+        if len(tensors) != self.world:
+            raise ValueError(f"need {self.world} tensors (one per virtual rank)")
+        for t in tensors:
+            _check_tensor(t)
+        return (ctypes.c_void_p * self.world)(*[t.data_ptr() for t in tensors])
+
+    def allreduce(self, tensors, scale=None, wire_dtype=None, algo=ALGO_AUTO, stream=None):
+        d, w = _wire(tensors[0], wire_dtype)
+        n = tensors[0].numel()
+        if any(t.numel() != n or t.dtype != tensors[0].dtype for t in tensors):
+            raise ValueError("all ranks must pass the same count and dtype")
+        if scale is None:
+            scale = 1.0 / self.world
+        _lib.check(self._lib.b2c_group_allreduce(self._arr, self._ptrs(tensors), n, d, w, ctypes.c_float(scale),
+                                                 algo, _stream_ptr(stream)))
+        return tensors
+
+    def broadcast(self, tensors, root=0, stream=None):
+        nbytes = tensors[0].numel() * tensors[0].element_size()
+        if any(t.numel() * t.element_size() != nbytes for t in tensors):
+            raise ValueError("all ranks must pass the same byte count")
+        _lib.check(self._lib.b2c_group_broadcast(self._arr, self._ptrs(tensors), nbytes, int(root),
+                                                 _stream_ptr(stream)))
+        return tensors
+
+    def barrier(self, stream=None):
+        _lib.check(self._lib.b2c_group_barrier(self._arr, _stream_ptr(stream)))
+
+    def close(self):
+        if getattr(self, "_open", False):
+            self._open = False
+            _lib.check(self._lib.b2c_group_destroy_local(self._arr, self.world))
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,578 @@
+// b2c host side: the C-ABI declared in include/b2c.h.
+// Plain CUDA runtime only — no torch, no NCCL, no C++ types across the boundary.
+#include <stdio.h>
+#include <stdarg.h>
+#include <string.h>
+#include <stdlib.h>
+#include <unistd.h>
+
+#include "b2c_kernels.cuh"
+
+// ---------------------------------------------------------------- errors
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+static int cuda_fail(cudaError_t e, const char* what) {
+  snprintf(g_err, sizeof(g_err), "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+  return (int)e;
+}
+#define CU(call)                                         \
+  do {                                                   \
+    cudaError_t e_ = (call);                             \
+    if (e_ != cudaSuccess) return cuda_fail(e_, #call);  \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) ok = (cudaSetDevice(dev) == cudaSuccess);
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+// ---------------------------------------------------------------- comm
+#define B2C_MAGIC 0x62326331u /* "b2c1" */
+
+struct ExportBlob {
+  uint32_t magic;
+  uint32_t version;
+  int32_t rank;
+  int32_t world;
+  int64_t pid;
+  int32_t device;       // CUDA ordinal in the exporting process
+  int32_t pad0;
+  uint64_t region_bytes;
+  uint64_t slot_bytes;
+  uint64_t raw_ptr;     // valid only inside the exporting process
+  uint64_t host_id;     // gethostid ^ boot-id hash: IPC handles do not cross nodes
+  unsigned char uuid[16];
+  cudaIpcMemHandle_t handle;  // 64 bytes
+};
+static_assert(sizeof(ExportBlob) <= B2C_EXPORT_BLOB_BYTES, "blob too large");
+
+struct b2c_comm {
+  int rank, world, device;
+  size_t arena_bytes, slot_bytes, region_bytes;
+  char* region;                      // local allocation
+  char* peer_region[B2C_MAX_WORLD];  // every rank's region as mapped here ([rank] == region)
+  bool peer_ipc[B2C_MAX_WORLD];      // opened with cudaIpcOpenMemHandle (must be closed)
+  uint32_t* status_h;                // pinned, mapped: sticky device-side error words
+  uint32_t* status_d;
+  bool ready;
+  bool local_group;
+  b2c_comm** group;                  // local group: all members (owned by member 0)
+  long params[B2C_PARAM__COUNT];
+  b2c_stats stats;
+};
+
+static uint64_t host_identity() {
+  uint64_t h = (uint64_t)gethostid();
+  FILE* f = fopen("/proc/sys/kernel/random/boot_id", "r");
+  if (f) {
+    char buf[64] = {0};
+    if (fgets(buf, sizeof(buf), f))
+      for (const char* p = buf; *p; ++p) h = h * 1099511628211ull ^ (unsigned char)*p;
+    fclose(f);
+  }
+  return h;
+}
+
+static void default_params(b2c_comm* c) {
+  c->params[B2C_PARAM_CROSSOVER_BYTES] = 512 * 1024;
+  c->params[B2C_PARAM_MAX_BLOCKS_ONESHOT] = 32;
+  c->params[B2C_PARAM_MAX_BLOCKS_TWOSHOT] = 64;
+  c->params[B2C_PARAM_THREADS] = 512;
+  c->params[B2C_PARAM_TIMEOUT_MS] = 10000;
+  c->params[B2C_PARAM_TWOSHOT_VARIANT] = 0;
+  c->params[B2C_PARAM_MAX_BLOCKS_BCAST] = 32;
+}
+
+static int comm_alloc(int rank, int world, int device, size_t arena_bytes, b2c_comm** out) {
+  if (!out) return fail(B2C_EINVAL, "b2c_comm_create: out is NULL");
+  *out = nullptr;
+  if (world < 1 || world > B2C_MAX_WORLD)
+    return fail(B2C_EINVAL, "b2c_comm_create: world=%d outside 1..%d (one NVSwitch domain)", world, B2C_MAX_WORLD);
+  if (rank < 0 || rank >= world) return fail(B2C_EINVAL, "b2c_comm_create: rank=%d outside 0..%d", rank, world - 1);
+  if (arena_bytes < 2 * 4096) return fail(B2C_EINVAL, "b2c_comm_create: arena_bytes=%zu too small (min 8192)", arena_bytes);
+  DeviceGuard g(device);
+  if (!g.ok) return fail(B2C_EINVAL, "b2c_comm_create: cannot select CUDA device %d", device);
+  b2c_comm* c = (b2c_comm*)calloc(1, sizeof(b2c_comm));
+  if (!c) return fail(B2C_EINVAL, "out of host memory");
+  c->rank = rank; c->world = world; c->device = device;
+  c->slot_bytes = (arena_bytes / 2) & ~(size_t)255;
+  c->arena_bytes = 2 * c->slot_bytes;
+  c->region_bytes = B2C_HEADER_BYTES + c->arena_bytes;
+  default_params(c);
+  cudaError_t e = cudaMalloc((void**)&c->region, c->region_bytes);
+  if (e != cudaSuccess) { free(c); return cuda_fail(e, "cudaMalloc(region)"); }
+  e = cudaMemset(c->region, 0, B2C_HEADER_BYTES);
+  if (e == cudaSuccess) e = cudaHostAlloc((void**)&c->status_h, 64, cudaHostAllocMapped);
+  if (e == cudaSuccess) { memset(c->status_h, 0, 64); e = cudaHostGetDevicePointer((void**)&c->status_d, c->status_h, 0); }
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    cudaFree(c->region);
+    if (c->status_h) cudaFreeHost(c->status_h);
+    free(c);
+    return cuda_fail(e, "b2c_comm_create: region set-up");
+  }
+  c->peer_region[rank] = c->region;
+  *out = c;
+  return B2C_OK;
+}
+
+extern "C" int b2c_version(void) { return B2C_VERSION; }
+extern "C" const char* b2c_last_error(void) { return g_err; }
+
+extern "C" int b2c_comm_create(int rank, int world, int device, size_t arena_bytes, b2c_comm** out) {
+  int rc = comm_alloc(rank, world, device, arena_bytes, out);
+  if (rc == B2C_OK && world == 1) (*out)->ready = true;  // nothing to import
+  return rc;
+}
+
+extern "C" int b2c_comm_export(b2c_comm* c, void* blob, size_t* len) {
+  if (!c || !blob || !len) return fail(B2C_EINVAL, "b2c_comm_export: NULL argument");
+  if (*len < B2C_EXPORT_BLOB_BYTES) return fail(B2C_EINVAL, "b2c_comm_export: blob needs %d bytes, got %zu", B2C_EXPORT_BLOB_BYTES, *len);
+  if (c->local_group) return fail(B2C_ESTATE, "b2c_comm_export: local groups are not exportable");
+  DeviceGuard g(c->device);
+  ExportBlob b;
+  memset(&b, 0, sizeof(b));
+  b.magic = B2C_MAGIC; b.version = B2C_VERSION;
+  b.rank = c->rank; b.world = c->world; b.pid = (int64_t)getpid(); b.device = c->device;
+  b.region_bytes = c->region_bytes; b.slot_bytes = c->slot_bytes;
+  b.raw_ptr = (uint64_t)(uintptr_t)c->region;
+  b.host_id = host_identity();
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, c->device));
+  memcpy(b.uuid, &prop.uuid, 16);
+  CU(cudaIpcGetMemHandle(&b.handle, c->region));
+  memset(blob, 0, B2C_EXPORT_BLOB_BYTES);
+  memcpy(blob, &b, sizeof(b));
+  *len = B2C_EXPORT_BLOB_BYTES;
+  return B2C_OK;
+}
+
+extern "C" int b2c_comm_import(b2c_comm* c, const void* blobs, size_t len_each) {
+  if (!c || !blobs) return fail(B2C_EINVAL, "b2c_comm_import: NULL argument");
+  if (len_each < sizeof(ExportBlob)) return fail(B2C_EINVAL, "b2c_comm_import: len_each=%zu too small", len_each);
+  if (c->local_group) return fail(B2C_ESTATE, "b2c_comm_import: local groups need no import");
+  if (c->ready && c->world > 1) return fail(B2C_ESTATE, "b2c_comm_import: already imported");
+  DeviceGuard g(c->device);
+  const uint64_t me_host = host_identity();
+  for (int q = 0; q < c->world; ++q) {
+    ExportBlob b;
+    memcpy(&b, (const char*)blobs + (size_t)q * len_each, sizeof(b));
+    if (b.magic != B2C_MAGIC || b.version != B2C_VERSION)
+      return fail(B2C_EINVAL, "b2c_comm_import: blob %d has bad magic/version", q);
+    if (b.rank != q || b.world != c->world)
+      return fail(B2C_EINVAL, "b2c_comm_import: blob %d is rank %d of %d; blobs must be in rank order", q, b.rank, b.world);
+    if (b.slot_bytes != c->slot_bytes)
+      return fail(B2C_EINVAL, "b2c_comm_import: rank %d arena slot %llu B != ours %zu B (arena must be symmetric)", q, (unsigned long long)b.slot_bytes, c->slot_bytes);
+    if (q == c->rank) continue;
+    if (b.host_id != me_host)
+      return fail(B2C_ENOPEER, "b2c_comm_import: rank %d is on another node; b2c is single NVSwitch domain only", q);
+    if (b.pid == (int64_t)getpid()) {
+      // peer lives in this process (one process driving several GPUs): direct peer access
+      if (b.device != c->device) {
+        int can = 0;
+        CU(cudaDeviceCanAccessPeer(&can, c->device, b.device));
+        if (!can) return fail(B2C_ENOPEER, "b2c_comm_import: device %d cannot access peer device %d", c->device, b.device);
+        cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceEnablePeerAccess");
+      }
+      c->peer_region[q] = (char*)(uintptr_t)b.raw_ptr;
+      c->peer_ipc[q] = false;
+    } else {
+      void* p = nullptr;
+      cudaError_t e = cudaIpcOpenMemHandle(&p, b.handle, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        snprintf(g_err, sizeof(g_err), "b2c_comm_import: cudaIpcOpenMemHandle(rank %d): %s (%s)", q, cudaGetErrorName(e), cudaGetErrorString(e));
+        return (int)e;
+      }
+      c->peer_region[q] = (char*)p;
+      c->peer_ipc[q] = true;
+    }
+  }
+  c->ready = true;
+  return B2C_OK;
+}
+
+extern "C" int b2c_comm_destroy(b2c_comm* c) {
+  if (!c) return B2C_OK;
+  if (c->local_group) return fail(B2C_ESTATE, "b2c_comm_destroy: member of a local group; use b2c_group_destroy_local");
+  DeviceGuard g(c->device);
+  cudaDeviceSynchronize();
+  int rc = B2C_OK;
+  for (int q = 0; q < c->world; ++q)
+    if (q != c->rank && c->peer_ipc[q] && c->peer_region[q]) {
+      cudaError_t e = cudaIpcCloseMemHandle(c->peer_region[q]);
+      if (e != cudaSuccess && rc == B2C_OK) rc = cuda_fail(e, "cudaIpcCloseMemHandle");
+    }
+  if (c->region) cudaFree(c->region);
+  if (c->status_h) cudaFreeHost(c->status_h);
+  free(c);
+  return rc;
+}
+
+extern "C" int b2c_group_create_local(int world, int device, size_t arena_bytes, b2c_comm** out) {
+  if (!out) return fail(B2C_EINVAL, "b2c_group_create_local: out is NULL");
+  if (world < 1 || world > B2C_MAX_WORLD) return fail(B2C_EINVAL, "b2c_group_create_local: world=%d outside 1..%d", world, B2C_MAX_WORLD);
+  b2c_comm** members = (b2c_comm**)calloc(world, sizeof(b2c_comm*));
+  for (int r = 0; r < world; ++r) {
+    int rc = comm_alloc(r, world, device, arena_bytes, &members[r]);
+    if (rc != B2C_OK) {
+      for (int k = 0; k < r; ++k) { members[k]->local_group = false; b2c_comm_destroy(members[k]); }
+      free(members);
+      return rc;
+    }
+  }
+  for (int r = 0; r < world; ++r) {
+    for (int q = 0; q < world; ++q) members[r]->peer_region[q] = members[q]->region;
+    members[r]->local_group = true;
+    members[r]->group = members;
+    members[r]->ready = true;
+    out[r] = members[r];
+  }
+  return B2C_OK;
+}
+
+extern "C" int b2c_group_destroy_local(b2c_comm** comms, int world) {
+  if (!comms || world < 1) return B2C_OK;
+  b2c_comm** members = comms[0] ? comms[0]->group : nullptr;
+  for (int r = 0; r < world; ++r)
+    if (comms[r]) { comms[r]->local_group = false; b2c_comm_destroy(comms[r]); comms[r] = nullptr; }
+  free(members);
+  return B2C_OK;
+}
+
+// ---------------------------------------------------------------- launch helpers
+template <int MODE> static const void* oneshot_fn(int W) {
+  switch (W) {
+    case 1: return (const void*)k_allreduce_oneshot<MODE, 1>;
+    case 2: return (const void*)k_allreduce_oneshot<MODE, 2>;
+    case 3: return (const void*)k_allreduce_oneshot<MODE, 3>;
+    case 4: return (const void*)k_allreduce_oneshot<MODE, 4>;
+    case 5: return (const void*)k_allreduce_oneshot<MODE, 5>;
+    case 6: return (const void*)k_allreduce_oneshot<MODE, 6>;
+    case 7: return (const void*)k_allreduce_oneshot<MODE, 7>;
+    default: return (const void*)k_allreduce_oneshot<MODE, 8>;
+  }
+}
+template <int MODE> static const void* twoshot_fn(int W) {
+  switch (W) {
+    case 1: return (const void*)k_allreduce_twoshot<MODE, 1>;
+    case 2: return (const void*)k_allreduce_twoshot<MODE, 2>;
+    case 3: return (const void*)k_allreduce_twoshot<MODE, 3>;
+    case 4: return (const void*)k_allreduce_twoshot<MODE, 4>;
+    case 5: return (const void*)k_allreduce_twoshot<MODE, 5>;
+    case 6: return (const void*)k_allreduce_twoshot<MODE, 6>;
+    case 7: return (const void*)k_allreduce_twoshot<MODE, 7>;
+    default: return (const void*)k_allreduce_twoshot<MODE, 8>;
+  }
+}
+
+static int check_sticky(b2c_comm* c) {
+  if (c->status_h && c->status_h[0] != 0)
+    return fail(-(int)c->status_h[0], "b2c: comm is dead: flag barrier timed out earlier (epoch %u, channel %u, waiting for rank %u)",
+                c->status_h[1], c->status_h[2], c->status_h[3]);
+  return B2C_OK;
+}
+
+// geometry: identical on every rank because it depends on (size, params) only
+static void geometry(const b2c_comm* c, size_t nvec_span, long max_blocks, int* nblocks, int* threads, uint32_t* chunk_vecs) {
+  long th = c->params[B2C_PARAM_THREADS];
+  if (max_blocks < 1) max_blocks = 1;
+  if (max_blocks > B2C_MAX_BLOCKS) max_blocks = B2C_MAX_BLOCKS;
+  size_t per_block_min = (size_t)th;
+  size_t cu = (nvec_span + per_block_min * max_blocks - 1) / (per_block_min * max_blocks);
+  if (cu < 1) cu = 1;
+  if (cu > 8) cu = 8;
+  size_t cv = per_block_min * cu;
+  size_t nb = (nvec_span + cv - 1) / cv;
+  if (nb < 1) nb = 1;
+  if (nb > (size_t)max_blocks) nb = max_blocks;
+  *nblocks = (int)nb; *threads = (int)th; *chunk_vecs = (uint32_t)cv;
+}
+
+// local group: all W virtual ranks' CTAs must be co-resident (cooperative launch), so the
+// per-rank channel count is capped at (resident CTAs on the device) / W
+static long group_block_cap(const b2c_comm* c, const void* fn, long want) {
+  int per_sm = 0, sms = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, (int)c->params[B2C_PARAM_THREADS], 0) != cudaSuccess ||
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device) != cudaSuccess) {
+    cudaGetLastError();
+    return want;
+  }
+  long cap = (long)per_sm * sms / c->world;
+  if (cap < 1) cap = 1;
+  return want < cap ? want : cap;
+}
+
+struct Launch {
+  const void* fn;
+  B2cKArgs args;
+  int nblocks, threads;
+};
+
+static int do_launch(b2c_comm* lead, Launch& L, int grid_y, cudaStream_t stream) {
+  void* params[] = {(void*)&L.args};
+  dim3 grid(L.nblocks, grid_y), block(L.threads);
+  cudaError_t e;
+  if (grid_y > 1) {
+    // all virtual ranks' CTAs must be co-resident: they wait on one another
+    e = cudaLaunchCooperativeKernel(L.fn, grid, block, params, 0, stream);
+  } else {
+    e = cudaLaunchKernel(L.fn, grid, block, params, 0, stream);
+  }
+  if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, "kernel launch"); }
+  lead->stats.launches++;
+  lead->stats.last_blocks = L.nblocks;
+  lead->stats.last_threads = L.threads;
+  return B2C_OK;
+}
+
+static void fill_common(b2c_comm* c, B2cKArgs& a, bool group) {
+  memset(&a, 0, sizeof(a));
+  for (int q = 0; q < c->world; ++q) a.region[q] = c->peer_region[q];
+  if (group) {
+    for (int q = 0; q < c->world; ++q) a.status[q] = c->group[q]->status_d;
+    a.rank = -1;
+  } else {
+    a.status[c->rank] = c->status_d;
+    a.rank = c->rank;
+  }
+  a.world = c->world;
+  a.slot_bytes = c->slot_bytes;
+  a.timeout_ns = (unsigned long long)c->params[B2C_PARAM_TIMEOUT_MS] * 1000000ull;
+  a.variant = (int)c->params[B2C_PARAM_TWOSHOT_VARIANT];
+}
+
+static int mode_of(int dtype, int wire, int* mode, int* vw, int* ub) {
+  if (dtype == B2C_F32 && wire == B2C_F32) { *mode = MODE_F32; *vw = 4; *ub = 4; return 0; }
+  if (dtype == B2C_BF16 && wire == B2C_BF16) { *mode = MODE_BF16; *vw = 8; *ub = 2; return 0; }
+  if (dtype == B2C_F32 && wire == B2C_BF16) { *mode = MODE_F32_BF16; *vw = 8; *ub = 4; return 0; }
+  return fail(B2C_EUNSUPPORTED, "b2c_allreduce: (dtype=%d, wire_dtype=%d) unsupported; use (F32,F32), (BF16,BF16) or (F32,BF16)", dtype, wire);
+}
+
+// one allreduce, possibly split into several launches when it exceeds an arena slot.
+// bufs: group ? per-rank buffers : only bufs[c->rank] is used
+static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t count, int dtype, int wire,
+                          float scale, int algo, cudaStream_t stream) {
+  if (!c) return fail(B2C_EINVAL, "b2c_allreduce: comm is NULL");
+  if (!c->ready) return fail(B2C_ESTATE, "b2c_allreduce: comm not imported yet (call b2c_comm_import on every rank)");
+  int rc = check_sticky(c);
+  if (rc) return rc;
+  int mode, vw, ub;
+  rc = mode_of(dtype, wire, &mode, &vw, &ub);
+  if (rc) return rc;
+  if (algo < B2C_ALGO_AUTO || algo > B2C_ALGO_TWOSHOT) return fail(B2C_EINVAL, "b2c_allreduce: algo=%d", algo);
+  c->stats.calls_allreduce++;
+  c->stats.bytes_allreduce += (uint64_t)count * ub;
+  if (count == 0) return B2C_OK;
+  const int W = c->world;
+  for (int r = 0; r < W; ++r) {
+    if (!group && r != c->rank) continue;
+    if (!bufs[r]) return fail(B2C_EINVAL, "b2c_allreduce: buf is NULL");
+    if ((uintptr_t)bufs[r] % ub) return fail(B2C_EINVAL, "b2c_allreduce: buf %p is not aligned to its element size %d", bufs[r], ub);
+  }
+  DeviceGuard g(c->device);
+  const size_t slot_vecs = c->slot_bytes / 16;
+  const size_t piece_elems = slot_vecs * vw;  // keeps every piece 16-byte aligned relative to buf
+  for (size_t off = 0; off < count; off += piece_elems) {
+    const size_t n = (count - off < piece_elems) ? count - off : piece_elems;
+    const size_t nvec = (n + vw - 1) / vw;
+    int use = algo;
+    if (W == 1) use = B2C_ALGO_ONESHOT;
+    else if (use == B2C_ALGO_AUTO) use = (nvec * 16 <= (size_t)c->params[B2C_PARAM_CROSSOVER_BYTES]) ? B2C_ALGO_ONESHOT : B2C_ALGO_TWOSHOT;
+    Launch L;
+    fill_common(c, L.args, group);
+    for (int r = 0; r < W; ++r)
+      if (group || r == c->rank) L.args.buf[r] = (char*)bufs[r] + off * ub;
+    L.args.count = n;
+    L.args.scale = scale;
+    if (use == B2C_ALGO_ONESHOT) {
+      L.fn = mode == MODE_F32 ? oneshot_fn<MODE_F32>(W) : mode == MODE_BF16 ? oneshot_fn<MODE_BF16>(W) : oneshot_fn<MODE_F32_BF16>(W);
+      long mb = c->params[B2C_PARAM_MAX_BLOCKS_ONESHOT];
+      if (group) mb = group_block_cap(c, L.fn, mb);
+      geometry(c, nvec, mb, &L.nblocks, &L.threads, &L.args.chunk_vecs);
+      c->stats.oneshot_launches++;
+    } else {
+      const size_t nvs = (nvec + W - 1) / W;
+      L.fn = mode == MODE_F32 ? twoshot_fn<MODE_F32>(W) : mode == MODE_BF16 ? twoshot_fn<MODE_BF16>(W) : twoshot_fn<MODE_F32_BF16>(W);
+      long mb = c->params[B2C_PARAM_MAX_BLOCKS_TWOSHOT];
+      if (group) mb = group_block_cap(c, L.fn, mb);
+      geometry(c, nvs, mb, &L.nblocks, &L.threads, &L.args.chunk_vecs);
+      c->stats.twoshot_launches++;
+    }
+    c->stats.last_algo = use;
+    rc = do_launch(c, L, group ? W : 1, stream);
+    if (rc) return rc;
+  }
+  return B2C_OK;
+}
+
+static int broadcast_impl(b2c_comm* c, void* const* bufs, bool group, size_t bytes, int root, cudaStream_t stream) {
+  if (!c) return fail(B2C_EINVAL, "b2c_broadcast: comm is NULL");
+  if (!c->ready) return fail(B2C_ESTATE, "b2c_broadcast: comm not imported yet");
+  if (root < 0 || root >= c->world) return fail(B2C_EINVAL, "b2c_broadcast: root=%d outside 0..%d", root, c->world - 1);
+  int rc = check_sticky(c);
+  if (rc) return rc;
+  c->stats.calls_broadcast++;
+  c->stats.bytes_broadcast += bytes;
+  if (bytes == 0 || c->world == 1) return B2C_OK;
+  for (int r = 0; r < c->world; ++r)
+    if ((group || r == c->rank) && !bufs[r]) return fail(B2C_EINVAL, "b2c_broadcast: buf is NULL");
+  DeviceGuard g(c->device);
+  const size_t piece = c->slot_bytes;
+  for (size_t off = 0; off < bytes; off += piece) {
+    const size_t n = (bytes - off < piece) ? bytes - off : piece;
+    Launch L;
+    fill_common(c, L.args, group);
+    for (int r = 0; r < c->world; ++r)
+      if (group || r == c->rank) L.args.buf[r] = (char*)bufs[r] + off;
+    L.args.count = n;
+    L.args.root = root;
+    L.fn = (const void*)k_broadcast;
+    long mb = c->params[B2C_PARAM_MAX_BLOCKS_BCAST];
+    if (group) mb = group_block_cap(c, L.fn, mb);
+    geometry(c, (n + 15) / 16, mb, &L.nblocks, &L.threads, &L.args.chunk_vecs);
+    rc = do_launch(c, L, group ? c->world : 1, stream);
+    if (rc) return rc;
+  }
+  return B2C_OK;
+}
+
+static int barrier_impl(b2c_comm* c, bool group, cudaStream_t stream) {
+  if (!c) return fail(B2C_EINVAL, "b2c_barrier: comm is NULL");
+  if (!c->ready) return fail(B2C_ESTATE, "b2c_barrier: comm not imported yet");
+  int rc = check_sticky(c);
+  if (rc) return rc;
+  c->stats.calls_barrier++;
+  DeviceGuard g(c->device);
+  Launch L;
+  fill_common(c, L.args, group);
+  L.nblocks = 1; L.threads = 32; L.args.chunk_vecs = 32;
+  L.fn = (const void*)k_barrier;
+  return do_launch(c, L, group ? c->world : 1, stream);
+}
+
+// ---------------------------------------------------------------- C-ABI data path
+extern "C" int b2c_allreduce(b2c_comm* c, void* buf, size_t count, int dtype, int wire_dtype, float scale,
+                             int algo, b2c_stream_t stream) {
+  if (c && c->local_group) return fail(B2C_ESTATE, "b2c_allreduce: comm belongs to a local group; use b2c_group_allreduce");
+  void* bufs[B2C_MAX_WORLD] = {0};
+  if (c && c->rank >= 0 && c->rank < B2C_MAX_WORLD) bufs[c->rank] = buf;
+  return allreduce_impl(c, bufs, false, count, dtype, wire_dtype, scale, algo, (cudaStream_t)stream);
+}
+extern "C" int b2c_broadcast(b2c_comm* c, void* buf, size_t bytes, int root, b2c_stream_t stream) {
+  if (c && c->local_group) return fail(B2C_ESTATE, "b2c_broadcast: comm belongs to a local group; use b2c_group_broadcast");
+  void* bufs[B2C_MAX_WORLD] = {0};
+  if (c && c->rank >= 0 && c->rank < B2C_MAX_WORLD) bufs[c->rank] = buf;
+  return broadcast_impl(c, bufs, false, bytes, root, (cudaStream_t)stream);
+}
+extern "C" int b2c_barrier(b2c_comm* c, b2c_stream_t stream) {
+  if (c && c->local_group) return fail(B2C_ESTATE, "b2c_barrier: comm belongs to a local group; use b2c_group_barrier");
+  return barrier_impl(c, false, (cudaStream_t)stream);
+}
+
+static int group_check(b2c_comm** comms, const char* who) {
+  if (!comms || !comms[0]) return fail(B2C_EINVAL, "%s: comms is NULL", who);
+  if (!comms[0]->local_group) return fail(B2C_ESTATE, "%s: not a local group", who);
+  return B2C_OK;
+}
+extern "C" int b2c_group_allreduce(b2c_comm** comms, void** bufs, size_t count, int dtype, int wire_dtype,
+                                   float scale, int algo, b2c_stream_t stream) {
+  int rc = group_check(comms, "b2c_group_allreduce");
+  if (rc) return rc;
+  if (!bufs) return fail(B2C_EINVAL, "b2c_group_allreduce: bufs is NULL");
+  return allreduce_impl(comms[0], bufs, true, count, dtype, wire_dtype, scale, algo, (cudaStream_t)stream);
+}
+extern "C" int b2c_group_broadcast(b2c_comm** comms, void** bufs, size_t bytes, int root, b2c_stream_t stream) {
+  int rc = group_check(comms, "b2c_group_broadcast");
+  if (rc) return rc;
+  if (!bufs) return fail(B2C_EINVAL, "b2c_group_broadcast: bufs is NULL");
+  return broadcast_impl(comms[0], bufs, true, bytes, root, (cudaStream_t)stream);
+}
+extern "C" int b2c_group_barrier(b2c_comm** comms, b2c_stream_t stream) {
+  int rc = group_check(comms, "b2c_group_barrier");
+  if (rc) return rc;
+  return barrier_impl(comms[0], true, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------- knobs
+extern "C" int b2c_set_param(b2c_comm* c, int key, long v) {
+  if (!c) return fail(B2C_EINVAL, "b2c_set_param: comm is NULL");
+  if (key < 0 || key >= B2C_PARAM__COUNT) return fail(B2C_EINVAL, "b2c_set_param: unknown key %d", key);
+  switch (key) {
+    case B2C_PARAM_THREADS:
+      if (v < 128 || v > 512 || v % 32) return fail(B2C_EINVAL, "b2c_set_param: threads=%ld must be 128..512, multiple of 32", v);
+      break;
+    case B2C_PARAM_MAX_BLOCKS_ONESHOT:
+    case B2C_PARAM_MAX_BLOCKS_TWOSHOT:
+    case B2C_PARAM_MAX_BLOCKS_BCAST:
+      if (v < 1 || v > B2C_MAX_BLOCKS) return fail(B2C_EINVAL, "b2c_set_param: blocks=%ld must be 1..%d", v, B2C_MAX_BLOCKS);
+      break;
+    case B2C_PARAM_TIMEOUT_MS:
+      if (v < 1) return fail(B2C_EINVAL, "b2c_set_param: timeout_ms=%ld must be >= 1", v);
+      break;
+    case B2C_PARAM_TWOSHOT_VARIANT:
+      if (v != 0 && v != 1) return fail(B2C_EINVAL, "b2c_set_param: twoshot variant %ld (0 = push, 1 = pull)", v);
+      break;
+    case B2C_PARAM_CROSSOVER_BYTES:
+      if (v < 0) return fail(B2C_EINVAL, "b2c_set_param: crossover=%ld", v);
+      break;
+  }
+  if (c->local_group && c->group) {
+    for (int r = 0; r < c->world; ++r) c->group[r]->params[key] = v;
+  } else {
+    c->params[key] = v;
+  }
+  return B2C_OK;
+}
+extern "C" int b2c_get_param(b2c_comm* c, int key, long* v) {
+  if (!c || !v) return fail(B2C_EINVAL, "b2c_get_param: NULL argument");
+  if (key < 0 || key >= B2C_PARAM__COUNT) return fail(B2C_EINVAL, "b2c_get_param: unknown key %d", key);
+  *v = c->params[key];
+  return B2C_OK;
+}
+extern "C" int b2c_get_stats(b2c_comm* c, b2c_stats* out) {
+  if (!c || !out) return fail(B2C_EINVAL, "b2c_get_stats: NULL argument");
+  *out = c->stats;
+  uint32_t st[4] = {0, 0, 0, 0};
+  if (c->local_group && c->group) {
+    for (int r = 0; r < c->world; ++r)
+      if (c->group[r]->status_h[0]) { memcpy(st, c->group[r]->status_h, sizeof(st)); break; }
+  } else if (c->status_h) {
+    memcpy(st, c->status_h, sizeof(st));
+  }
+  out->device_status = st[0];
+  out->device_status_detail[0] = st[1];
+  out->device_status_detail[1] = st[2];
+  out->device_status_detail[2] = st[3];
+  return B2C_OK;
+}
+extern "C" int b2c_comm_arena(b2c_comm* c, void** base, size_t* slot_bytes) {
+  if (!c) return fail(B2C_EINVAL, "b2c_comm_arena: comm is NULL");
+  if (base) *base = c->region + B2C_HEADER_BYTES;
+  if (slot_bytes) *slot_bytes = c->slot_bytes;
+  return B2C_OK;
+}
+extern "C" int b2c_comm_info(b2c_comm* c, int* rank, int* world, int* device) {
+  if (!c) return fail(B2C_EINVAL, "b2c_comm_info: comm is NULL");
+  if (rank) *rank = c->rank;
+  if (world) *world = c->world;
+  if (device) *device = c->device;
+  return B2C_OK;
+}

@@ -1,0 +1,493 @@
+// b2c device code: cross-GPU reduce / broadcast kernels for sm_100a.
+//
+// One symmetric region per rank (exported with CUDA IPC, mapped by every peer):
+//
+//   [0, 4096)        control words (local use only): epoch, call counter, exit ticket
+//   [4096, 8192)     flag page: flags[block][src_rank] (u32, monotonic epochs,
+//                    written remotely by `src_rank`, spun on locally)
+//   [16384, +slot)   arena slot 0   } double buffered by call parity, so a rank that
+//   [.., +slot)      arena slot 1   } runs one call ahead never clobbers data a peer still reads
+//
+// Every CTA is an independent channel: CTA b of rank r only ever exchanges data
+// with CTA b of the peers (same chunk -> CTA mapping on every rank), so the only
+// cross-GPU synchronisation is a per-CTA flag barrier; there is no grid-wide sync.
+//
+// Data that another GPU may have written is always read with ld.relaxed.sys
+// (never the non-coherent path, never a possibly-stale L1 line); flags use
+// st.release.sys / ld.acquire.sys.  Sums are accumulated in fp32 in FIXED rank
+// order 0..W-1 on every rank, so replicas stay bitwise identical.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#include "../../include/b2c.h"
+
+#define B2C_CTL_BYTES 4096
+#define B2C_FLAG_BYTES 4096
+#define B2C_HEADER_BYTES 16384
+#define B2C_CTL_EPOCH 0
+#define B2C_CTL_CALLS 1
+#define B2C_CTL_TICKET 2
+
+enum { MODE_F32 = 0, MODE_BF16 = 1, MODE_F32_BF16 = 2, MODE_U8 = 3 };
+
+struct B2cKArgs {
+  void* buf[B2C_MAX_WORLD];        // caller buffer per rank (real mode: only [rank] is valid)
+  char* region[B2C_MAX_WORLD];     // rank q's symmetric region as mapped in this process
+  uint32_t* status[B2C_MAX_WORLD]; // sticky error words (host-mapped) per rank (real: only [rank])
+  size_t count;                    // caller elements (bytes for MODE_U8)
+  size_t slot_bytes;
+  unsigned long long timeout_ns;
+  float scale;
+  int rank;                        // >= 0: this launch is one rank; -1: rank = blockIdx.y (local group)
+  int world;
+  int root;
+  int variant;
+  uint32_t chunk_vecs;             // ownership granularity (16-byte vectors), multiple of blockDim.x
+};
+
+// ---------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// 16-byte load that is coherent with writes from other GPUs (bypasses L1)
+__device__ __forceinline__ uint4 ld_sys_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p));
+  return v;
+}
+// 16-byte store, no L1 allocation (streaming; may target a peer GPU)
+__device__ __forceinline__ void st_v4(void* p, uint4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// ---------------------------------------------------------------- per-mode traits
+template <int MODE> struct Mode;
+template <> struct Mode<MODE_F32> { static constexpr int VW = 4; static constexpr int UB = 4; };
+template <> struct Mode<MODE_BF16> { static constexpr int VW = 8; static constexpr int UB = 2; };
+template <> struct Mode<MODE_F32_BF16> { static constexpr int VW = 8; static constexpr int UB = 4; };
+template <> struct Mode<MODE_U8> { static constexpr int VW = 16; static constexpr int UB = 1; };
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);  // round-to-nearest-even, once
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+
+// caller buffer -> one 16-byte wire vector (vector g covers caller elements [g*VW, g*VW+VW))
+template <int MODE>
+__device__ __forceinline__ uint4 load_user(const void* buf, size_t g, size_t count, bool fast) {
+  constexpr int VW = Mode<MODE>::VW;
+  const size_t e0 = g * VW;
+  if (fast && e0 + VW <= count) {
+    if (MODE == MODE_F32_BF16) {
+      const uint4* p = reinterpret_cast<const uint4*>(static_cast<const float*>(buf) + e0);
+      uint4 a = p[0], b = p[1];
+      uint4 r;
+      r.x = pack_bf16x2(__uint_as_float(a.x), __uint_as_float(a.y));
+      r.y = pack_bf16x2(__uint_as_float(a.z), __uint_as_float(a.w));
+      r.z = pack_bf16x2(__uint_as_float(b.x), __uint_as_float(b.y));
+      r.w = pack_bf16x2(__uint_as_float(b.z), __uint_as_float(b.w));
+      return r;
+    } else {
+      return *reinterpret_cast<const uint4*>(static_cast<const char*>(buf) + e0 * Mode<MODE>::UB);
+    }
+  }
+  // ragged tail or misaligned base: element by element, zero filled past `count`
+  uint32_t w[4] = {0u, 0u, 0u, 0u};
+  if (MODE == MODE_F32) {
+    const float* p = static_cast<const float*>(buf);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (e0 + k < count) w[k] = __float_as_uint(p[e0 + k]);
+  } else if (MODE == MODE_BF16) {
+    const unsigned short* p = static_cast<const unsigned short*>(buf);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (e0 + k < count) w[k >> 1] |= (uint32_t)p[e0 + k] << ((k & 1) * 16);
+  } else if (MODE == MODE_F32_BF16) {
+    const float* p = static_cast<const float*>(buf);
+    float f[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = (e0 + k < count) ? p[e0 + k] : 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) w[k] = pack_bf16x2(f[2 * k], f[2 * k + 1]);
+  } else {
+    const unsigned char* p = static_cast<const unsigned char*>(buf);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+      if (e0 + k < count) w[k >> 2] |= (uint32_t)p[e0 + k] << ((k & 3) * 8);
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// one 16-byte wire vector -> caller buffer (never writes past `count`)
+template <int MODE>
+__device__ __forceinline__ void store_user(void* buf, size_t g, size_t count, bool fast, uint4 v) {
+  constexpr int VW = Mode<MODE>::VW;
+  const size_t e0 = g * VW;
+  if (fast && e0 + VW <= count) {
+    if (MODE == MODE_F32_BF16) {
+      uint4* p = reinterpret_cast<uint4*>(static_cast<float*>(buf) + e0);
+      p[0] = make_uint4(v.x << 16, v.x & 0xffff0000u, v.y << 16, v.y & 0xffff0000u);
+      p[1] = make_uint4(v.z << 16, v.z & 0xffff0000u, v.w << 16, v.w & 0xffff0000u);
+    } else {
+      *reinterpret_cast<uint4*>(static_cast<char*>(buf) + e0 * Mode<MODE>::UB) = v;
+    }
+    return;
+  }
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  if (MODE == MODE_F32) {
+    float* p = static_cast<float*>(buf);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (e0 + k < count) p[e0 + k] = __uint_as_float(w[k]);
+  } else if (MODE == MODE_BF16) {
+    unsigned short* p = static_cast<unsigned short*>(buf);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (e0 + k < count) p[e0 + k] = (unsigned short)(w[k >> 1] >> ((k & 1) * 16));
+  } else if (MODE == MODE_F32_BF16) {
+    float* p = static_cast<float*>(buf);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (e0 + k < count)
+        p[e0 + k] = (k & 1) ? bf16_hi(w[k >> 1]) : bf16_lo(w[k >> 1]);
+  } else {
+    unsigned char* p = static_cast<unsigned char*>(buf);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+      if (e0 + k < count) p[e0 + k] = (unsigned char)(w[k >> 2] >> ((k & 3) * 8));
+  }
+}
+
+// fp32 accumulator over one wire vector.  Every term is scaled first (its own rounding:
+// exactly tensor.div_(W) of the reference hook when W is a power of two, so overflow /
+// underflow behave like the reference), terms are added in the order given (rank order),
+// and the result is rounded once to the wire type.  No FMA contraction (__fmul_rn/__fadd_rn).
+template <int MODE> struct Acc {
+  static constexpr int VW = Mode<MODE>::VW;
+  float a[VW];
+  __device__ __forceinline__ void unpack(uint4 v, float* f) const {
+    if (MODE == MODE_F32) {
+      f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y);
+      f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
+    } else {
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { f[2 * k] = bf16_lo(w[k]); f[2 * k + 1] = bf16_hi(w[k]); }
+    }
+  }
+  __device__ __forceinline__ void init(uint4 v, float scale) {  // first term: no add to +0 (keeps -0)
+    float f[VW];
+    unpack(v, f);
+#pragma unroll
+    for (int k = 0; k < VW; ++k) a[k] = __fmul_rn(f[k], scale);
+  }
+  __device__ __forceinline__ void add(uint4 v, float scale) {
+    float f[VW];
+    unpack(v, f);
+#pragma unroll
+    for (int k = 0; k < VW; ++k) a[k] = __fadd_rn(a[k], __fmul_rn(f[k], scale));
+  }
+  __device__ __forceinline__ uint4 finish() const {
+    if (MODE == MODE_F32) {
+      return make_uint4(__float_as_uint(a[0]), __float_as_uint(a[1]), __float_as_uint(a[2]), __float_as_uint(a[3]));
+    } else {
+      return make_uint4(pack_bf16x2(a[0], a[1]), pack_bf16x2(a[2], a[3]),
+                        pack_bf16x2(a[4], a[5]), pack_bf16x2(a[6], a[7]));
+    }
+  }
+};
+
+// ---------------------------------------------------------------- per-CTA context
+struct Ctx {
+  int rank;
+  int b;            // channel (blockIdx.x)
+  int nb;           // channels (gridDim.x)
+  uint32_t epoch;   // flags reach epoch+1 / epoch+2 in this call
+  uint32_t calls;
+  size_t slot_off;  // byte offset of the active arena slot in every region
+  uint32_t* ctl;
+  bool dead;        // a barrier timed out: skip the remaining phases
+};
+
+__device__ __forceinline__ int* dead_flag() {
+  __shared__ int s_dead;  // sticky for the whole launch; zeroed once in prologue()
+  return &s_dead;
+}
+
+__device__ __forceinline__ Ctx prologue(const B2cKArgs& a) {
+  Ctx c;
+  if (threadIdx.x == 0) *dead_flag() = 0;
+  __syncthreads();
+  c.rank = a.rank >= 0 ? a.rank : (int)blockIdx.y;
+  c.b = blockIdx.x;
+  c.nb = gridDim.x;
+  c.ctl = reinterpret_cast<uint32_t*>(a.region[c.rank]);
+  c.epoch = ld_volatile_u32(c.ctl + B2C_CTL_EPOCH);
+  c.calls = ld_volatile_u32(c.ctl + B2C_CTL_CALLS);
+  c.slot_off = (size_t)B2C_HEADER_BYTES + (size_t)(c.calls & 1u) * a.slot_bytes;
+  c.dead = false;
+  return c;
+}
+
+// last CTA out advances the epoch / call counters for the next launch on this stream
+__device__ __forceinline__ void epilogue(const Ctx& c) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned t = atomicAdd(c.ctl + B2C_CTL_TICKET, 1u);
+    if (t == (unsigned)c.nb - 1u) {
+      c.ctl[B2C_CTL_TICKET] = 0u;
+      c.ctl[B2C_CTL_EPOCH] = c.epoch + 2u;
+      c.ctl[B2C_CTL_CALLS] = c.calls + 1u;
+      __threadfence();
+    }
+  }
+}
+
+// Per-channel cross-GPU barrier.  Thread q (< world) publishes `target` into peer q's
+// flag page (release: orders every write this CTA made before the __syncthreads) and
+// then spins on the word peer q writes into OUR page (acquire).  Bounded spin: on
+// timeout the sticky status word is set and the CTA skips the rest of the call.
+__device__ __forceinline__ void channel_barrier(const B2cKArgs& a, Ctx& c, uint32_t target) {
+  int* s_dead = dead_flag();
+  __syncthreads();
+  if ((int)threadIdx.x < a.world) {
+    const int q = threadIdx.x;
+    uint32_t* theirs = reinterpret_cast<uint32_t*>(a.region[q] + B2C_CTL_BYTES) + c.b * B2C_MAX_WORLD + c.rank;
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(a.region[c.rank] + B2C_CTL_BYTES) + c.b * B2C_MAX_WORLD + q;
+    st_release_sys(theirs, target);
+    unsigned long long t0 = 0;
+    unsigned spins = 0;
+    while ((int)(ld_acquire_sys(mine) - target) < 0) {
+      if ((++spins & 0xffu) == 0u) {
+        unsigned long long now = globaltimer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > a.timeout_ns) {
+          volatile uint32_t* st = a.status[c.rank];
+          if (st[0] == 0u) {
+            st[1] = target; st[2] = (uint32_t)c.b; st[3] = (uint32_t)q;
+            st[0] = (uint32_t)(-B2C_ETIMEOUT);
+            __threadfence_system();
+          }
+          *s_dead = 1;
+          break;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (*s_dead) c.dead = true;
+}
+
+// iterate vectors i of [0, n) owned by channel c.b, U at a time per thread.
+// BODY(idx[U], pred[U]) must be a callable; chunks of a.chunk_vecs are dealt round-robin.
+#define B2C_FOR_OWNED(n_, U_, ...)                                                            \
+  for (size_t c0_ = (size_t)c.b * a.chunk_vecs; c0_ < (n_); c0_ += (size_t)c.nb * a.chunk_vecs) { \
+    const size_t c1_ = (c0_ + a.chunk_vecs < (n_)) ? c0_ + a.chunk_vecs : (n_);                \
+    for (size_t i_ = c0_ + threadIdx.x; i_ < c1_; i_ += (size_t)blockDim.x * (U_)) {          \
+      size_t idx[U_]; bool pred[U_];                                                         \
+      _Pragma("unroll") for (int u = 0; u < (U_); ++u) {                                      \
+        idx[u] = i_ + (size_t)u * blockDim.x; pred[u] = idx[u] < c1_;                         \
+      }                                                                                      \
+      __VA_ARGS__                                                                            \
+    }                                                                                        \
+  }
+
+template <int W> struct Unroll { static constexpr int U = (W >= 8) ? 2 : (W >= 4) ? 4 : (W >= 2) ? 8 : 8; };
+template <> struct Unroll<3> { static constexpr int U = 4; };
+template <> struct Unroll<5> { static constexpr int U = 3; };
+template <> struct Unroll<6> { static constexpr int U = 2; };
+template <> struct Unroll<7> { static constexpr int U = 2; };
+
+// ================================================================= one-shot allreduce
+// stage own bucket -> arena; barrier; every rank pulls all W copies of the vectors its
+// channel owns, adds them in rank order, scales, rounds once, writes its own buffer.
+template <int MODE, int W>
+__global__ void __launch_bounds__(512, 1) k_allreduce_oneshot(const __grid_constant__ B2cKArgs a) {
+  constexpr int VW = Mode<MODE>::VW;
+  constexpr int U = Unroll<W>::U;
+  Ctx c = prologue(a);
+  void* buf = a.buf[c.rank];
+  const size_t count = a.count;
+  const size_t nvec = (count + VW - 1) / VW;
+  const bool fast = ((reinterpret_cast<uintptr_t>(buf) & 15u) == 0);
+
+  if (W == 1) {
+    // single rank: out = in * scale (rounded once); nothing crosses a link, no arena pass
+    B2C_FOR_OWNED(nvec, 8, {
+      uint4 v[8];
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = load_user<MODE>(buf, idx[u], count, fast);
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) {
+        Acc<MODE> acc; acc.init(v[u], a.scale);
+        store_user<MODE>(buf, idx[u], count, fast, acc.finish());
+      }
+    })
+    epilogue(c);
+    return;
+  }
+
+  char* my_slot = a.region[c.rank] + c.slot_off;
+  B2C_FOR_OWNED(nvec, 8, {
+    uint4 v[8];
+    _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = load_user<MODE>(buf, idx[u], count, fast);
+    _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) st_v4(my_slot + idx[u] * 16, v[u]);
+  })
+  channel_barrier(a, c, c.epoch + 1u);
+  if (!c.dead) {
+    const char* src[W];
+#pragma unroll
+    for (int q = 0; q < W; ++q) src[q] = a.region[q] + c.slot_off;
+    B2C_FOR_OWNED(nvec, U, {
+      uint4 v[U][W];
+      _Pragma("unroll") for (int u = 0; u < U; ++u)
+        _Pragma("unroll") for (int q = 0; q < W; ++q)
+          if (pred[u]) v[u][q] = ld_sys_v4(src[q] + idx[u] * 16);
+      _Pragma("unroll") for (int u = 0; u < U; ++u) if (pred[u]) {
+        Acc<MODE> acc; acc.init(v[u][0], a.scale);
+        _Pragma("unroll") for (int q = 1; q < W; ++q) acc.add(v[u][q], a.scale);
+        store_user<MODE>(buf, idx[u], count, fast, acc.finish());
+      }
+    })
+  }
+  epilogue(c);
+}
+
+// ================================================================= two-shot allreduce
+// stage -> barrier A -> rank r reduces shard r from all W arenas (reduce-scatter) and
+//   variant 0: pushes the finished vectors into every peer's arena (in place; only rank r
+//              ever reads shard r of any arena), writes its own buffer directly
+//   variant 1: writes them into its own arena + buffer
+// -> barrier B -> copy the W-1 foreign shards into the caller buffer from the local arena
+//   (variant 0) or pulled from the owning peer (variant 1).
+template <int MODE, int W>
+__global__ void __launch_bounds__(512, 1) k_allreduce_twoshot(const __grid_constant__ B2cKArgs a) {
+  constexpr int VW = Mode<MODE>::VW;
+  constexpr int U = Unroll<W>::U;
+  Ctx c = prologue(a);
+  void* buf = a.buf[c.rank];
+  const size_t count = a.count;
+  const size_t nvec = (count + VW - 1) / VW;
+  const size_t nvs = (nvec + W - 1) / W;  // vectors per shard (last shards may be short / empty)
+  const bool fast = ((reinterpret_cast<uintptr_t>(buf) & 15u) == 0);
+  char* my_slot = a.region[c.rank] + c.slot_off;
+
+  // phase 0: stage. Channel b stages slice b of EVERY shard, because channel b of rank r'
+  // will read exactly slice b of shard r' from us.
+  for (int r = 0; r < W; ++r) {
+    const size_t s0 = (size_t)r * nvs;
+    if (s0 >= nvec) break;
+    const size_t sl = (s0 + nvs <= nvec) ? nvs : nvec - s0;
+    B2C_FOR_OWNED(sl, 8, {
+      uint4 v[8];
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = load_user<MODE>(buf, s0 + idx[u], count, fast);
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) st_v4(my_slot + (s0 + idx[u]) * 16, v[u]);
+    })
+  }
+  channel_barrier(a, c, c.epoch + 1u);
+
+  // phase 1: reduce my shard
+  if (!c.dead) {
+    const size_t s0 = (size_t)c.rank * nvs;
+    const size_t sl = (s0 >= nvec) ? 0 : ((s0 + nvs <= nvec) ? nvs : nvec - s0);
+    char* slot[W];
+#pragma unroll
+    for (int q = 0; q < W; ++q) slot[q] = a.region[q] + c.slot_off + s0 * 16;
+    const int variant = a.variant;
+    B2C_FOR_OWNED(sl, U, {
+      uint4 v[U][W];
+      _Pragma("unroll") for (int u = 0; u < U; ++u)
+        _Pragma("unroll") for (int q = 0; q < W; ++q)
+          if (pred[u]) v[u][q] = ld_sys_v4(slot[q] + idx[u] * 16);
+      _Pragma("unroll") for (int u = 0; u < U; ++u) if (pred[u]) {
+        Acc<MODE> acc; acc.init(v[u][0], a.scale);
+        _Pragma("unroll") for (int q = 1; q < W; ++q) acc.add(v[u][q], a.scale);
+        const uint4 res = acc.finish();
+        store_user<MODE>(buf, s0 + idx[u], count, fast, res);
+        if (variant == 0) {
+          _Pragma("unroll") for (int k = 1; k < W; ++k) {  // rotate targets so peers are hit evenly
+            int q = c.rank + k; if (q >= W) q -= W;
+            st_v4(a.region[q] + c.slot_off + (s0 + idx[u]) * 16, res);
+          }
+        } else {
+          st_v4(my_slot + (s0 + idx[u]) * 16, res);
+        }
+      }
+    })
+  }
+  channel_barrier(a, c, c.epoch + 2u);
+
+  // phase 2: gather the other shards into the caller buffer
+  if (!c.dead) {
+    for (int k = 1; k < W; ++k) {
+      int r = c.rank + k; if (r >= W) r -= W;
+      const size_t s0 = (size_t)r * nvs;
+      if (s0 >= nvec) continue;
+      const size_t sl = (s0 + nvs <= nvec) ? nvs : nvec - s0;
+      const char* src = (a.variant == 0 ? my_slot : a.region[r] + c.slot_off) + s0 * 16;
+      B2C_FOR_OWNED(sl, 8, {
+        uint4 v[8];
+        _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = ld_sys_v4(src + idx[u] * 16);
+        _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) store_user<MODE>(buf, s0 + idx[u], count, fast, v[u]);
+      })
+    }
+  }
+  epilogue(c);
+}
+
+// ================================================================= broadcast (bit exact)
+// root stages its bytes into its arena; barrier; every other rank pulls them.
+__global__ void __launch_bounds__(512, 1) k_broadcast(const __grid_constant__ B2cKArgs a) {
+  Ctx c = prologue(a);
+  void* buf = a.buf[c.rank];
+  const size_t count = a.count;
+  const size_t nvec = (count + 15) / 16;
+  const bool fast = ((reinterpret_cast<uintptr_t>(buf) & 15u) == 0);
+  char* root_slot = a.region[a.root] + c.slot_off;
+  if (c.rank == a.root) {
+    B2C_FOR_OWNED(nvec, 8, {
+      uint4 v[8];
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = load_user<MODE_U8>(buf, idx[u], count, fast);
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) st_v4(root_slot + idx[u] * 16, v[u]);
+    })
+  }
+  channel_barrier(a, c, c.epoch + 1u);
+  if (!c.dead && c.rank != a.root) {
+    B2C_FOR_OWNED(nvec, 8, {
+      uint4 v[8];
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = ld_sys_v4(root_slot + idx[u] * 16);
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) store_user<MODE_U8>(buf, idx[u], count, fast, v[u]);
+    })
+  }
+  epilogue(c);
+}
+
+// ================================================================= barrier
+__global__ void __launch_bounds__(32, 1) k_barrier(const __grid_constant__ B2cKArgs a) {
+  Ctx c = prologue(a);
+  channel_barrier(a, c, c.epoch + 1u);
+  epilogue(c);
+}
