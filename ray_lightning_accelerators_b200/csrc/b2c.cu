@@ -309,13 +309,25 @@ static void geometry(const b2c_comm* c, size_t nvec_span, long max_blocks, int* 
 // local group: all W virtual ranks' CTAs must be co-resident (cooperative launch), so the
 // per-rank channel count is capped at (resident CTAs on the device) / W
 static long group_block_cap(const b2c_comm* c, const void* fn, long want) {
-  int per_sm = 0, sms = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, (int)c->params[B2C_PARAM_THREADS], 0) != cudaSuccess ||
-      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device) != cudaSuccess) {
-    cudaGetLastError();
-    return want;
+  // tiny cache: the occupancy query costs microseconds of host time per call
+  static thread_local struct { const void* fn; int threads, device, resident; } cache[8];
+  static thread_local int cache_n = 0;
+  const int threads = (int)c->params[B2C_PARAM_THREADS];
+  int resident = -1;
+  for (int i = 0; i < cache_n; ++i)
+    if (cache[i].fn == fn && cache[i].threads == threads && cache[i].device == c->device) resident = cache[i].resident;
+  if (resident < 0) {
+    int per_sm = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, 0) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device) != cudaSuccess) {
+      cudaGetLastError();
+      return want;
+    }
+    resident = per_sm * sms;
+    cache[cache_n % 8] = {fn, threads, c->device, resident};
+    if (cache_n < 8) cache_n++;
   }
-  long cap = (long)per_sm * sms / c->world;
+  long cap = (long)resident / c->world;
   if (cap < 1) cap = 1;
   return want < cap ? want : cap;
 }

@@ -1,0 +1,158 @@
+"""Where the b2c kernels plug into torch DDP — the worker-side half of the hot path.
+
+Reference call sites replaced:
+  C2  initial parameter/buffer broadcast inside the DDP constructor
+      (torch:nn/parallel/distributed.py:879-890, reached from ray_ddp.py:218-219)
+      -> ``broadcast_module_states`` after constructing DDP with init_sync=False
+  C3  per-bucket gradient allreduce of the c10d Reducer
+      -> ``allreduce_hook`` registered with DDP.register_comm_hook
+  C4  per-forward buffer broadcast (_sync_buffers, distributed.py:2214-2257)
+      -> ``BufferSync`` forward pre-hook on ONE flat buffer (one launch per step)
+
+No NCCL on any of the three; the torch process group stays for control collectives (C9).
+"""
+import torch
+import torch.distributed as dist
+
+from .comm import ALGO_AUTO, Comm
+
+
+class B2cHookState:
+    """State object handed to DDP.register_comm_hook (the `state` of hook(state, bucket))."""
+
+    def __init__(self, comm, wire_dtype=None, algo=ALGO_AUTO):
+        self.comm = comm
+        self.wire_dtype = wire_dtype
+        self.algo = algo
+        # high-priority side stream: the reduce of bucket k overlaps the rest of backward
+        self.stream = torch.cuda.Stream(device=comm.device, priority=-1)
+        self.buckets_reduced = 0
+        self.timing = None  # optional list of (start_event, end_event, nbytes) filled by bench.py
+
+    def enable_timing(self):
+        self.timing = []
+
+
+def allreduce_hook(state, bucket):
+    """DDP communication hook: hook(state, bucket) -> Future[Tensor]
+    (torch:nn/parallel/distributed.py:1987-2067).  With a hook registered the bucket is NOT
+    pre-divided by world size (distributed.py:2021-2023); the kernel owns the 1/W.
+
+    Runs on the autograd engine thread.  Nothing here blocks the host: the comm stream waits
+    for the backward stream on the device, the kernel is enqueued, and the returned Future is
+    completed while the comm stream is current so torch records the event the Reducer waits on."""
+    buf = bucket.buffer()
+    comm = state.comm
+    wire = state.wire_dtype if (state.wire_dtype is not None and buf.dtype == torch.float32) else None
+    state.stream.wait_stream(torch.cuda.current_stream(buf.device))
+    with torch.cuda.stream(state.stream):
+        if state.timing is not None:
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record(state.stream)
+        comm.allreduce(buf, scale=1.0 / comm.world, wire_dtype=wire, algo=state.algo, stream=state.stream)
+        if state.timing is not None:
+            e1.record(state.stream)
+            state.timing.append((e0, e1, buf.numel() * buf.element_size()))
+        fut = torch.futures.Future(devices=[buf.device])
+        fut.set_result(buf)
+    state.buckets_reduced += 1
+    return fut
+
+
+def _flat_groups(tensors, cap_bytes):
+    """Group tensors by dtype into runs of at most cap_bytes (like _broadcast_coalesced's
+    250 MiB buffers, torch:distributed/utils.py:289-328)."""
+    by_dtype = {}
+    for t in tensors:
+        by_dtype.setdefault(t.dtype, []).append(t)
+    for dtype, ts in by_dtype.items():
+        run, size = [], 0
+        for t in ts:
+            nb = t.numel() * t.element_size()
+            if run and size + nb > cap_bytes:
+                yield run
+                run, size = [], 0
+            run.append(t)
+            size += nb
+        if run:
+            yield run
+
+
+@torch.no_grad()
+def broadcast_module_states(comm, module, root=0, cap_bytes=64 << 20, stream=None):
+    """C2: copy rank `root`'s parameters and buffers to every rank, bit for bit.
+    Coalesced: flatten -> one b2c_broadcast per <= cap_bytes run -> copy back."""
+    tensors = [p.data for p in module.parameters()] + [b.data for b in module.buffers()]
+    tensors = [t for t in tensors if t.is_cuda and t.numel() > 0]
+    nbytes = 0
+    for run in _flat_groups(tensors, cap_bytes):
+        flat = torch.cat([t.reshape(-1) for t in run])
+        comm.broadcast(flat, root=root, stream=stream)
+        off = 0
+        for t in run:
+            n = t.numel()
+            t.copy_(flat[off:off + n].view_as(t))
+            off += n
+        nbytes += flat.numel() * flat.element_size()
+    return nbytes
+
+
+class BufferSync:
+    """C4: the per-forward broadcast of module buffers (BatchNorm running stats,
+    num_batches_tracked) from rank 0.  At set-up every buffer is re-pointed at a slice of ONE
+    flat byte tensor (16-byte aligned slices), so the per-step work is a single kernel launch
+    with no flatten / unflatten copies; in-place updates by the modules keep the views valid."""
+
+    def __init__(self, comm, module, root=0):
+        self.comm, self.root = comm, root
+        bufs = [b for b in module.buffers() if b.is_cuda and b.numel() > 0]
+        self.count = len(bufs)
+        self.nbytes = 0
+        self.flat = None
+        if not bufs or comm.world == 1:
+            return
+        offs, total = [], 0
+        for b in bufs:
+            offs.append(total)
+            total += (b.numel() * b.element_size() + 15) // 16 * 16
+        self.flat = torch.zeros(total, dtype=torch.uint8, device=bufs[0].device)
+        with torch.no_grad():
+            for b, off in zip(bufs, offs):
+                nb = b.numel() * b.element_size()
+                view = self.flat[off:off + nb].view(b.dtype).view(b.shape)
+                view.copy_(b.data)
+                b.data = view
+        self.nbytes = total
+
+    def __call__(self, module=None, inputs=None):
+        if self.flat is not None:
+            self.comm.broadcast(self.flat, root=self.root)
+
+
+def wrap_ddp(model, comm, device_ids=None, wire_dtype=None, find_unused_parameters=True,
+             bucket_cap_mb=25, gradient_as_bucket_view=False, process_group=None):
+    """Build the DDP wrapper the way the reference's workers do (PTL 1.1.7 configure_ddp:
+    DistributedDataParallel(model, device_ids, find_unused_parameters=True), reached from
+    ray_ddp.py:218-219) with the three collectives re-routed to b2c."""
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    broadcast_module_states(comm, model, root=0)                 # C2 (instead of init_sync)
+    bufsync = BufferSync(comm, model, root=0)                    # C4 set-up (re-points buffers)
+    ddp = DDP(model, device_ids=device_ids, find_unused_parameters=find_unused_parameters,
+              bucket_cap_mb=bucket_cap_mb, gradient_as_bucket_view=gradient_as_bucket_view,
+              broadcast_buffers=False, init_sync=False, process_group=process_group)
+    state = B2cHookState(comm, wire_dtype=wire_dtype)
+    ddp.register_comm_hook(state, allreduce_hook)                # C3
+    if bufsync.flat is not None:
+        ddp.register_forward_pre_hook(bufsync)                   # C4 per step
+    ddp._b2c_state = state
+    ddp._b2c_bufsync = bufsync
+    return ddp
+
+
+def comm_from_default_group(arena_bytes=None):
+    """Create the b2c communicator over the already-initialised torch process group
+    (ray_ddp.py:232-237 creates it); the group only carries the 256-byte IPC blobs."""
+    if not dist.is_initialized():
+        raise RuntimeError("torch.distributed is not initialised; call init_ddp_connection first")
+    return Comm.from_process_group(arena_bytes=arena_bytes)

@@ -1,0 +1,166 @@
+"""Worker for tests/test_multigpu.py — one process per GPU under torchrun.  Checks the
+cross-process CUDA-IPC path over NVLink against (a) the kernels' contract (CPU oracle,
+bit-exact), (b) the reference path itself: torch.distributed NCCL all_reduce / broadcast and
+stock NCCL DDP on the same tensors (what RayAccelerator(use_gpu=True) executes,
+ray_lightning/ray_ddp.py:227)."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from examples import workloads  # noqa: E402
+from oracle import oracle as O  # noqa: E402
+from ray_lightning_accelerators_b200 import _lib, ddp_hook  # noqa: E402
+from ray_lightning_accelerators_b200.comm import ALGO_ONESHOT, ALGO_TWOSHOT, Comm  # noqa: E402
+
+ALGOS = [(ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1)]
+
+
+def bits(t):
+    return t.view(torch.int32 if t.element_size() == 4 else torch.int16)
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    hidden = os.environ.get("B2C_TEST_HIDE_DEVICES") == "1"
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    if hidden:
+        # Ray's GPU pinning: the actor sees ONE device, index 0 (tests/test_ddp_gpu.py:83-103)
+        os.environ["CUDA_VISIBLE_DEVICES"] = str(local)
+        local = 0
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    comm = Comm.from_process_group(arena_bytes=96 << 20)
+    comm.set_param(_lib.PARAM_TIMEOUT_MS, 5000)
+    dev = torch.device("cuda", local)
+
+    # ---- allreduce: contract (bit-exact) + NCCL (bit-exact at W=2 / int payloads, else 1e-6)
+    for kind in ("int", "randn", "wide"):
+        for n in (1, 5, 1000, 27882, 406568, 3103747):
+            grads = [O.payload(kind, n, r) for r in range(world)]
+            want = O.b2c_allreduce_f32(grads)
+            ref = torch.from_numpy(grads[rank]).to(dev).div_(world)
+            dist.all_reduce(ref)
+            for algo, variant in ALGOS:
+                comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
+                t = torch.from_numpy(grads[rank]).to(dev)
+                comm.allreduce(t, algo=algo)
+                torch.cuda.synchronize()
+                comm.check_alive()
+                got = t.cpu().numpy()
+                assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), ("contract", kind, n, algo, variant)
+                if world == 2 or (kind == "int" and world in (4, 8)):
+                    assert torch.equal(bits(t), bits(ref)), ("nccl bit-exact", kind, n, algo, variant)
+                else:
+                    denom = sum(np.abs(x.astype(np.float64)) for x in grads) / world
+                    assert O.rel_err(got, ref.cpu().numpy(), denom) <= 1e-6, ("nccl 1e-6", kind, n)
+    # ---- bf16 gradients and bf16 wire
+    for n in (9, 27882, 1 << 20):
+        gb = [O.to_bf16_bits(O.payload("randn", n, r)) for r in range(world)]
+        want = O.b2c_allreduce_bf16(gb)
+        for algo, variant in ALGOS:
+            comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
+            t = torch.from_numpy(gb[rank].view(np.int16).copy()).to(dev).view(torch.bfloat16)
+            comm.allreduce(t, algo=algo)
+            torch.cuda.synchronize()
+            assert np.array_equal(t.view(torch.int16).cpu().numpy().view(np.uint16), want), ("bf16", n, algo)
+        ref = torch.from_numpy(gb[rank].view(np.int16).copy()).to(dev).view(torch.bfloat16).div_(world)
+        dist.all_reduce(ref)
+        if world == 2:  # north_star: one bf16 ulp vs the reference path
+            assert O.bf16_ulp_diff(want, ref.view(torch.int16).cpu().numpy().view(np.uint16)).max() <= 1
+        grads = [O.payload("randn", n, r) for r in range(world)]
+        t = torch.from_numpy(grads[rank]).to(dev)
+        comm.allreduce(t, wire_dtype=torch.bfloat16, algo=ALGO_TWOSHOT)
+        torch.cuda.synchronize()
+        assert np.array_equal(t.cpu().numpy().view(np.uint32), O.b2c_allreduce_f32_bf16wire(grads).view(np.uint32))
+    # ---- broadcast: bit-exact vs NCCL broadcast, every root
+    for n in (1, 17, 111528, 212904, (5 << 20) + 3):
+        for root in range(world):
+            src = torch.from_numpy(np.random.default_rng(100 * root + rank).integers(0, 256, n, dtype=np.uint8)).to(dev)
+            a, b = src.clone(), src.clone()
+            dist.broadcast(a, src=root)
+            comm.broadcast(b, root=root)
+            torch.cuda.synchronize()
+            assert torch.equal(a, b), ("broadcast", n, root)
+    # ---- stress: 200 back-to-back calls, payload changes every call, no host sync
+    outs = []
+    for i in range(200):
+        algo, variant = ALGOS[i % 3]
+        comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
+        n = 1000 + 997 * (i % 50)
+        t = torch.full((n,), float(rank + i), device=dev)
+        comm.allreduce(t, algo=algo)
+        outs.append((t, sum(r + i for r in range(world)) / world))
+    torch.cuda.synchronize()
+    comm.check_alive()
+    for t, want in outs:
+        assert torch.allclose(t, torch.full_like(t, want), rtol=1e-6, atol=0), "stress"
+
+    # ---- DDP: our hook vs stock NCCL DDP, MLP (config #2) 100 steps, loss within 1e-5 relative
+    def train(use_b2c):
+        model = workloads.build_model("mnist_mlp", seed=0).to(dev)
+        if use_b2c:
+            ddp = ddp_hook.wrap_ddp(model, comm, device_ids=[local])
+        else:
+            ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], find_unused_parameters=True)
+        opt = model.configure_optimizers()
+        losses = []
+        for step in range(100):
+            x, y = workloads.synthetic_batch("mnist_mlp", 32, rank, step)
+            x, y = x.to(dev), y.to(dev)
+            opt.zero_grad(set_to_none=True)
+            loss = model.loss_fn(ddp(x), y)
+            loss.backward()
+            opt.step()
+            losses.append(loss.item())
+        params = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+        return np.array(losses), params
+
+    torch.backends.cudnn.deterministic = True
+    l_ref, p_ref = train(False)
+    l_b2c, p_b2c = train(True)
+    rel = np.abs(l_b2c - l_ref) / np.maximum(np.abs(l_ref), 1e-12)
+    assert rel.max() <= 1e-5, f"loss curve differs from NCCL DDP: {rel.max()}"
+    if world == 2:
+        assert np.array_equal(l_b2c, l_ref), "W=2: loss curves must be bit-identical to NCCL DDP"
+        assert torch.equal(p_b2c, p_ref)
+    p0 = p_b2c.clone()
+    dist.broadcast(p0, src=0)
+    assert torch.equal(p0, p_b2c), "replicas drifted"
+    # ---- a model with buffers: BatchNorm stats follow rank 0 (C4) like stock DDP
+    def train_bn(use_b2c):
+        torch.manual_seed(0)
+        m = torch.nn.Sequential(torch.nn.Linear(16, 16), torch.nn.BatchNorm1d(16), torch.nn.Linear(16, 4)).to(dev)
+        if use_b2c:
+            ddp = ddp_hook.wrap_ddp(m, comm, device_ids=[local])
+        else:
+            ddp = torch.nn.parallel.DistributedDataParallel(m, device_ids=[local], find_unused_parameters=True)
+        opt = torch.optim.SGD(m.parameters(), lr=0.05)
+        for step in range(20):
+            g = torch.Generator().manual_seed(step * 10 + rank)
+            x = torch.randn(8, 16, generator=g).to(dev)
+            opt.zero_grad()
+            ddp(x).square().mean().backward()
+            opt.step()
+        return torch.cat([t.detach().float().reshape(-1) for t in list(m.parameters()) + list(m.buffers())])
+
+    s_ref, s_b2c = train_bn(False), train_bn(True)
+    if world == 2:
+        assert torch.equal(s_ref, s_b2c), "BN model state differs from stock DDP"
+    else:
+        assert torch.allclose(s_ref, s_b2c, rtol=1e-5, atol=1e-7)
+
+    dist.barrier()
+    st = comm.stats()
+    comm.close()
+    dist.destroy_process_group()
+    if rank == 0:
+        print(f"MP_WORKER_OK world={world} hidden={hidden} launches={st['launches']}")
+
+
+if __name__ == "__main__":
+    main()

@@ -312,7 +312,7 @@ def test_full_size_buckets_properties(groups, world):
     """At BASELINE sizes the CPU oracle is too slow to run per case; use size-independent
     properties instead: (1) the torch fp32 restatement of the contract on the GPU
     (((g0*s)+(g1*s))+...) must match bit for bit, (2) identical inputs are a fixed point at
-    power-of-two W, (3) replicas are bitwise identical."""
+    W = 2, (3) replicas are bitwise identical."""
     g = groups(world, arena_bytes=160 << 20)
     for n in RESNET50_BUCKET_ELEMS:
         gen = torch.Generator(device=DEV).manual_seed(n)
@@ -328,10 +328,11 @@ def test_full_size_buckets_properties(groups, world):
             torch.cuda.synchronize()
             for t in ts:
                 assert torch.equal(t.view(torch.int32), want.view(torch.int32)), (n, algo, variant)
-        same = [grads[0].clone() for _ in range(world)]
-        g.allreduce(same, algo=ALGO_TWOSHOT)
-        torch.cuda.synchronize()
-        assert torch.equal(same[0], grads[0]) and torch.equal(same[-1], grads[0])
+        if world == 2:  # x/2 + x/2 == x exactly; for W > 2 partial sums like 3x/W need extra bits
+            same = [grads[0].clone() for _ in range(world)]
+            g.allreduce(same, algo=ALGO_TWOSHOT)
+            torch.cuda.synchronize()
+            assert torch.equal(same[0], grads[0]) and torch.equal(same[-1], grads[0])
     g.check_alive()
 
 

@@ -55,6 +55,7 @@ def main():
                     tot = 0.0
                     for _ in range(args.iters):
                         flush.fill_(1)  # L2 flush between timed launches
+                        torch.cuda._sleep(300000)  # keep the GPU busy so the host runs ahead of the stream
                         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                         e0.record()
                         g.allreduce(ts, algo=algo)
