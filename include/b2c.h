@@ -34,7 +34,7 @@ extern "C" {
 
 #define B2C_VERSION 100          /* 0.1.0 */
 #define B2C_MAX_WORLD 8          /* one NVSwitch domain */
-#define B2C_MAX_BLOCKS 128       /* independent flag channels per comm */
+#define B2C_MAX_BLOCKS 256       /* independent flag channels per comm */
 #define B2C_EXPORT_BLOB_BYTES 256
 
 typedef struct b2c_comm b2c_comm;

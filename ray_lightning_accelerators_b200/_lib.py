@@ -25,7 +25,7 @@ PARAM_TIMEOUT_MS = 4
 PARAM_TWOSHOT_VARIANT = 5
 PARAM_MAX_BLOCKS_BCAST = 6
 MAX_WORLD = 8
-MAX_BLOCKS = 128
+MAX_BLOCKS = 256
 EXPORT_BLOB_BYTES = 256
 E_INVAL, E_STATE, E_TOOBIG, E_TIMEOUT, E_NOPEER, E_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 

@@ -3,7 +3,7 @@
 // One symmetric region per rank (exported with CUDA IPC, mapped by every peer):
 //
 //   [0, 4096)        control words (local use only): epoch, call counter, exit ticket
-//   [4096, 8192)     flag page: flags[block][src_rank] (u32, monotonic epochs,
+//   [4096, 12288)    flag page: flags[block][src_rank] (u32, monotonic epochs,
 //                    written remotely by `src_rank`, spun on locally)
 //   [16384, +slot)   arena slot 0   } double buffered by call parity, so a rank that
 //   [.., +slot)      arena slot 1   } runs one call ahead never clobbers data a peer still reads
@@ -24,11 +24,13 @@
 #include "../../include/b2c.h"
 
 #define B2C_CTL_BYTES 4096
-#define B2C_FLAG_BYTES 4096
+#define B2C_FLAG_BYTES 8192
 #define B2C_HEADER_BYTES 16384
 #define B2C_CTL_EPOCH 0
 #define B2C_CTL_CALLS 1
 #define B2C_CTL_TICKET 2
+
+static_assert(B2C_MAX_BLOCKS * B2C_MAX_WORLD * 4 <= B2C_FLAG_BYTES && B2C_CTL_BYTES + B2C_FLAG_BYTES <= B2C_HEADER_BYTES, "flag page too small");
 
 enum { MODE_F32 = 0, MODE_BF16 = 1, MODE_F32_BF16 = 2, MODE_U8 = 3 };
 
