@@ -60,7 +60,11 @@ enum {
   B2C_PARAM_TIMEOUT_MS = 4,       /* bounded spin in the cross-GPU barrier */
   B2C_PARAM_TWOSHOT_VARIANT = 5,  /* 0 = pull-reduce + push (default), 1 = pull + pull */
   B2C_PARAM_MAX_BLOCKS_BCAST = 6,
-  B2C_PARAM__COUNT = 7
+  B2C_PARAM_ZEROCOPY = 7,         /* 1 (default): two-shot runs in place on registered / local-group
+                                     buffers with no staging; 0: always stage through the arena */
+  B2C_PARAM_ZEROCOPY_MIN_BYTES = 8, /* AUTO: at or above this size a registered buffer uses the
+                                     zero-copy two-shot even below the one-shot crossover */
+  B2C_PARAM__COUNT = 9
 };
 
 /* error codes */
@@ -83,6 +87,7 @@ typedef struct b2c_stats {
   uint64_t bytes_broadcast;
   uint64_t oneshot_launches;
   uint64_t twoshot_launches;
+  uint64_t zerocopy_launches;
   uint32_t last_algo;           /* B2C_ALGO_* actually used by the last allreduce */
   uint32_t last_blocks;         /* grid.x of the last launch */
   uint32_t last_threads;
@@ -148,6 +153,20 @@ int b2c_group_allreduce(b2c_comm** comms, void** bufs, size_t count, int dtype, 
                         float scale, int algo, b2c_stream_t stream);
 int b2c_group_broadcast(b2c_comm** comms, void** bufs, size_t bytes, int root, b2c_stream_t stream);
 int b2c_group_barrier(b2c_comm** comms, b2c_stream_t stream);
+
+/* ---- registered (zero-copy) buffers --------------------------------------
+ * A gradient bucket that lives in plain cudaMalloc memory (torch's caching allocator
+ * without expandable_segments) can be mapped into every peer once; b2c_allreduce then
+ * reduces it IN PLACE over NVLink with no staging pass through the arena.  Collective:
+ * every rank exports its buffer, the blobs are swapped (rank order) and imported.
+ * After that any b2c_allreduce whose [buf, buf+bytes) lies inside a registration — at the
+ * SAME offset on every rank — takes the zero-copy two-shot path when it is 16-byte
+ * aligned, (dtype == wire_dtype) and two-shot is selected.  No reference counterpart (NCCL
+ * user-buffer registration is the closest upstream analogue). */
+#define B2C_REG_BLOB_BYTES 128
+int b2c_register_export(b2c_comm* comm, void* ptr, size_t bytes, void* blob, size_t* len);
+int b2c_register_import(b2c_comm* comm, void* ptr, size_t bytes, const void* blobs, size_t len_each);
+int b2c_deregister(b2c_comm* comm, void* ptr);
 
 /* ---- knobs, counters, introspection ------------------------------------ */
 int b2c_set_param(b2c_comm* comm, int key, long value);

@@ -24,6 +24,9 @@ PARAM_THREADS = 3
 PARAM_TIMEOUT_MS = 4
 PARAM_TWOSHOT_VARIANT = 5
 PARAM_MAX_BLOCKS_BCAST = 6
+PARAM_ZEROCOPY = 7
+PARAM_ZEROCOPY_MIN_BYTES = 8
+REG_BLOB_BYTES = 128
 MAX_WORLD = 8
 MAX_BLOCKS = 256
 EXPORT_BLOB_BYTES = 256
@@ -52,6 +55,7 @@ class Stats(ctypes.Structure):
         ("bytes_broadcast", ctypes.c_uint64),
         ("oneshot_launches", ctypes.c_uint64),
         ("twoshot_launches", ctypes.c_uint64),
+        ("zerocopy_launches", ctypes.c_uint64),
         ("last_algo", ctypes.c_uint32),
         ("last_blocks", ctypes.c_uint32),
         ("last_threads", ctypes.c_uint32),
@@ -86,6 +90,9 @@ SIGNATURES = {
     "b2c_group_allreduce": (_int, [_pp, _pp, _sz, _int, _int, _c.c_float, _int, _vp]),
     "b2c_group_broadcast": (_int, [_pp, _pp, _sz, _int, _vp]),
     "b2c_group_barrier": (_int, [_pp, _vp]),
+    "b2c_register_export": (_int, [_vp, _vp, _sz, _vp, _c.POINTER(_sz)]),
+    "b2c_register_import": (_int, [_vp, _vp, _sz, _vp, _sz]),
+    "b2c_deregister": (_int, [_vp, _vp]),
     "b2c_set_param": (_int, [_vp, _int, _c.c_long]),
     "b2c_get_param": (_int, [_vp, _int, _c.POINTER(_c.c_long)]),
     "b2c_get_stats": (_int, [_vp, _c.POINTER(Stats)]),

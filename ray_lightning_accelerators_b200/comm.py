@@ -27,6 +27,8 @@ _ENV_PARAMS = {
     "B2C_THREADS": _lib.PARAM_THREADS,
     "B2C_TIMEOUT_MS": _lib.PARAM_TIMEOUT_MS,
     "B2C_TWOSHOT_VARIANT": _lib.PARAM_TWOSHOT_VARIANT,
+    "B2C_ZEROCOPY": _lib.PARAM_ZEROCOPY,
+    "B2C_ZEROCOPY_MIN_BYTES": _lib.PARAM_ZEROCOPY_MIN_BYTES,
 }
 
 
@@ -98,6 +100,8 @@ class Comm(_Base):
         _lib.check(self._lib.b2c_comm_create(self.rank, self.world, self.device, self.arena_bytes, ctypes.byref(h)))
         self._h = h
         self._first = h
+        self._exchange = exchange
+        self._registered = {}
         self._apply_env()
         if self.world > 1:
             if exchange is None:
@@ -130,6 +134,36 @@ class Comm(_Base):
             raise ValueError(f"need {self.world} blobs in rank order, got {len(blobs)}")
         joined = b"".join(bytes(b) for b in blobs)
         _lib.check(self._lib.b2c_comm_import(self._h, joined, len(joined) // self.world))
+
+    def register(self, t):
+        """Collective: map this tensor's memory into every peer so that allreduce can run in
+        place on it with no staging pass (zero-copy two-shot).  Every rank must call it with
+        its corresponding tensor (same size) in the same order.  Returns True when every rank
+        could export its buffer (plain cudaMalloc memory), False otherwise — the staged path
+        keeps working either way."""
+        _check_tensor(t)
+        key = (t.data_ptr(), t.numel() * t.element_size())
+        if key in self._registered:
+            return self._registered[key]
+        if self.world == 1:
+            self._registered[key] = False
+            return False
+        buf = ctypes.create_string_buffer(_lib.REG_BLOB_BYTES)
+        n = ctypes.c_size_t(_lib.REG_BLOB_BYTES)
+        rc = self._lib.b2c_register_export(self._h, ctypes.c_void_p(key[0]), key[1], buf, ctypes.byref(n))
+        blobs = self._exchange(buf.raw if rc == 0 else None)
+        ok = all(b is not None for b in blobs)
+        if ok:
+            joined = b"".join(bytes(b) for b in blobs)
+            _lib.check(self._lib.b2c_register_import(self._h, ctypes.c_void_p(key[0]), key[1], joined,
+                                                     _lib.REG_BLOB_BYTES))
+        self._registered[key] = ok
+        return ok
+
+    def deregister(self, t):
+        key = (t.data_ptr(), t.numel() * t.element_size())
+        if self._registered.pop(key, False):
+            _lib.check(self._lib.b2c_deregister(self._h, ctypes.c_void_p(key[0])))
 
     def allreduce(self, t, scale=None, wire_dtype=None, algo=ALGO_AUTO, stream=None):
         """In place: t = sum_r t_r * scale (default 1/world), fp32 accumulate in rank order."""

@@ -74,7 +74,34 @@ struct b2c_comm {
   b2c_comm** group;                  // local group: all members (owned by member 0)
   long params[B2C_PARAM__COUNT];
   b2c_stats stats;
+  struct Registration* regs;         // registered caller buffers (zero-copy path)
+  int nregs, regs_cap;
+  struct OpenedHandle* opened;       // IPC base allocations already mapped (one open per handle)
+  int nopened, opened_cap;
 };
+
+struct Registration {
+  char* local;                       // caller pointer on this rank
+  size_t bytes;
+  char* peer[B2C_MAX_WORLD];         // the same buffer of rank q, mapped here ([rank] == local)
+};
+struct OpenedHandle {
+  cudaIpcMemHandle_t handle;
+  char* base;
+  int refs;
+};
+struct RegBlob {
+  uint32_t magic;
+  int32_t rank;
+  int64_t pid;
+  int32_t device;
+  int32_t pad0;
+  uint64_t raw_ptr;
+  uint64_t offset;                   // ptr - base of its cudaMalloc allocation
+  uint64_t bytes;
+  cudaIpcMemHandle_t handle;         // of the base allocation
+};
+static_assert(sizeof(RegBlob) <= B2C_REG_BLOB_BYTES, "reg blob too large");
 
 static uint64_t host_identity() {
   uint64_t h = (uint64_t)gethostid();
@@ -96,6 +123,8 @@ static void default_params(b2c_comm* c) {
   c->params[B2C_PARAM_TIMEOUT_MS] = 10000;
   c->params[B2C_PARAM_TWOSHOT_VARIANT] = 0;
   c->params[B2C_PARAM_MAX_BLOCKS_BCAST] = 32;
+  c->params[B2C_PARAM_ZEROCOPY] = 1;
+  c->params[B2C_PARAM_ZEROCOPY_MIN_BYTES] = 256 * 1024;
 }
 
 static int comm_alloc(int rank, int world, int device, size_t arena_bytes, b2c_comm** out) {
@@ -220,6 +249,10 @@ extern "C" int b2c_comm_destroy(b2c_comm* c) {
       cudaError_t e = cudaIpcCloseMemHandle(c->peer_region[q]);
       if (e != cudaSuccess && rc == B2C_OK) rc = cuda_fail(e, "cudaIpcCloseMemHandle");
     }
+  for (int i = 0; i < c->nopened; ++i)
+    if (c->opened[i].base) cudaIpcCloseMemHandle(c->opened[i].base);
+  free(c->opened);
+  free(c->regs);
   if (c->region) cudaFree(c->region);
   if (c->status_h) cudaFreeHost(c->status_h);
   free(c);
@@ -281,6 +314,27 @@ template <int MODE> static const void* twoshot_fn(int W) {
     case 7: return (const void*)k_allreduce_twoshot<MODE, 7>;
     default: return (const void*)k_allreduce_twoshot<MODE, 8>;
   }
+}
+
+template <int MODE> static const void* twoshot_zc_fn(int W) {
+  switch (W) {
+    case 1: return (const void*)k_allreduce_twoshot_zc<MODE, 1>;
+    case 2: return (const void*)k_allreduce_twoshot_zc<MODE, 2>;
+    case 3: return (const void*)k_allreduce_twoshot_zc<MODE, 3>;
+    case 4: return (const void*)k_allreduce_twoshot_zc<MODE, 4>;
+    case 5: return (const void*)k_allreduce_twoshot_zc<MODE, 5>;
+    case 6: return (const void*)k_allreduce_twoshot_zc<MODE, 6>;
+    case 7: return (const void*)k_allreduce_twoshot_zc<MODE, 7>;
+    default: return (const void*)k_allreduce_twoshot_zc<MODE, 8>;
+  }
+}
+
+// registration covering [p, p+bytes), or NULL
+static Registration* find_reg(b2c_comm* c, const void* p, size_t bytes) {
+  const char* q = (const char*)p;
+  for (int i = 0; i < c->nregs; ++i)
+    if (q >= c->regs[i].local && q + bytes <= c->regs[i].local + c->regs[i].bytes) return &c->regs[i];
+  return nullptr;
 }
 
 static int check_sticky(b2c_comm* c) {
@@ -400,6 +454,37 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
     if ((uintptr_t)bufs[r] % ub) return fail(B2C_EINVAL, "b2c_allreduce: buf %p is not aligned to its element size %d", bufs[r], ub);
   }
   DeviceGuard g(c->device);
+
+  // ---- zero-copy two-shot: the buffers themselves are peer-visible (local group, or registered)
+  if (W > 1 && c->params[B2C_PARAM_ZEROCOPY] && mode != MODE_F32_BF16 && algo != B2C_ALGO_ONESHOT &&
+      (algo == B2C_ALGO_TWOSHOT || count * (size_t)ub >= (size_t)c->params[B2C_PARAM_ZEROCOPY_MIN_BYTES])) {
+    Registration* reg = group ? nullptr : find_reg(c, bufs[c->rank], count * (size_t)ub);
+    bool ok = group || reg != nullptr;
+    for (int r = 0; ok && r < W; ++r)
+      if ((group || r == c->rank) && ((uintptr_t)bufs[r] & 15u)) ok = false;
+    if (ok) {
+      Launch L;
+      fill_common(c, L.args, group);
+      if (group) {
+        for (int r = 0; r < W; ++r) L.args.buf[r] = bufs[r];
+      } else {
+        const size_t roff = (char*)bufs[c->rank] - reg->local;  // same offset on every rank (contract)
+        for (int r = 0; r < W; ++r) L.args.buf[r] = reg->peer[r] + roff;
+      }
+      L.args.count = count;
+      L.args.scale = scale;
+      const size_t nvs = (count / vw + W - 1) / W;
+      L.fn = mode == MODE_F32 ? twoshot_zc_fn<MODE_F32>(W) : twoshot_zc_fn<MODE_BF16>(W);
+      long mb = c->params[B2C_PARAM_MAX_BLOCKS_TWOSHOT];
+      if (group) mb = group_block_cap(c, L.fn, mb);
+      geometry(c, nvs, mb, &L.nblocks, &L.threads, &L.args.chunk_vecs);
+      c->stats.twoshot_launches++;
+      c->stats.zerocopy_launches++;
+      c->stats.last_algo = B2C_ALGO_TWOSHOT;
+      return do_launch(c, L, group ? W : 1, stream);
+    }
+  }
+
   const size_t slot_vecs = c->slot_bytes / 16;
   const size_t piece_elems = slot_vecs * vw;  // keeps every piece 16-byte aligned relative to buf
   for (size_t off = 0; off < count; off += piece_elems) {
@@ -523,6 +608,117 @@ extern "C" int b2c_group_barrier(b2c_comm** comms, b2c_stream_t stream) {
   return barrier_impl(comms[0], true, (cudaStream_t)stream);
 }
 
+// ---------------------------------------------------------------- registered buffers
+typedef int (*cuMemGetAddressRange_t)(unsigned long long* pbase, size_t* psize, unsigned long long dptr);
+
+static int alloc_base_of(void* ptr, char** base, size_t* size) {
+  static cuMemGetAddressRange_t fn = nullptr;
+  if (!fn) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    cudaError_t e = cudaGetDriverEntryPoint("cuMemGetAddressRange", &sym, cudaEnableDefault, &qr);
+    if (e != cudaSuccess || !sym) { cudaGetLastError(); return fail(B2C_EUNSUPPORTED, "cuMemGetAddressRange is not available from this driver"); }
+    fn = (cuMemGetAddressRange_t)sym;
+  }
+  unsigned long long b = 0;
+  size_t sz = 0;
+  int rc = fn(&b, &sz, (unsigned long long)(uintptr_t)ptr);
+  if (rc != 0) return fail(B2C_EINVAL, "b2c_register: %p is not inside a CUDA allocation (driver error %d)", ptr, rc);
+  *base = (char*)(uintptr_t)b;
+  *size = sz;
+  return B2C_OK;
+}
+
+extern "C" int b2c_register_export(b2c_comm* c, void* ptr, size_t bytes, void* blob, size_t* len) {
+  if (!c || !ptr || !blob || !len) return fail(B2C_EINVAL, "b2c_register_export: NULL argument");
+  if (*len < B2C_REG_BLOB_BYTES) return fail(B2C_EINVAL, "b2c_register_export: blob needs %d bytes", B2C_REG_BLOB_BYTES);
+  if (c->local_group) return fail(B2C_ESTATE, "b2c_register_export: local groups are zero-copy without registration");
+  DeviceGuard g(c->device);
+  char* base = nullptr;
+  size_t size = 0;
+  int rc = alloc_base_of(ptr, &base, &size);
+  if (rc) return rc;
+  if ((char*)ptr + bytes > base + size) return fail(B2C_EINVAL, "b2c_register_export: [%p, +%zu) crosses the end of its allocation", ptr, bytes);
+  RegBlob b;
+  memset(&b, 0, sizeof(b));
+  b.magic = B2C_MAGIC ^ 0x5a5a5a5au;
+  b.rank = c->rank; b.pid = (int64_t)getpid(); b.device = c->device;
+  b.raw_ptr = (uint64_t)(uintptr_t)ptr;
+  b.offset = (uint64_t)((char*)ptr - base);
+  b.bytes = bytes;
+  cudaError_t e = cudaIpcGetMemHandle(&b.handle, base);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail((int)e, "b2c_register_export: cudaIpcGetMemHandle(%p): %s — memory from cudaMallocAsync / expandable_segments "
+                "cannot be exported; the staged path stays available", base, cudaGetErrorName(e));
+  }
+  memset(blob, 0, B2C_REG_BLOB_BYTES);
+  memcpy(blob, &b, sizeof(b));
+  *len = B2C_REG_BLOB_BYTES;
+  return B2C_OK;
+}
+
+static int open_base(b2c_comm* c, const cudaIpcMemHandle_t& h, char** base) {
+  for (int i = 0; i < c->nopened; ++i)
+    if (memcmp(&c->opened[i].handle, &h, sizeof(h)) == 0) { c->opened[i].refs++; *base = c->opened[i].base; return B2C_OK; }
+  void* p = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, "b2c_register_import: cudaIpcOpenMemHandle"); }
+  if (c->nopened == c->opened_cap) {
+    c->opened_cap = c->opened_cap ? 2 * c->opened_cap : 16;
+    c->opened = (OpenedHandle*)realloc(c->opened, c->opened_cap * sizeof(OpenedHandle));
+  }
+  c->opened[c->nopened].handle = h;
+  c->opened[c->nopened].base = (char*)p;
+  c->opened[c->nopened].refs = 1;
+  c->nopened++;
+  *base = (char*)p;
+  return B2C_OK;
+}
+
+extern "C" int b2c_register_import(b2c_comm* c, void* ptr, size_t bytes, const void* blobs, size_t len_each) {
+  if (!c || !ptr || !blobs) return fail(B2C_EINVAL, "b2c_register_import: NULL argument");
+  if (len_each < sizeof(RegBlob)) return fail(B2C_EINVAL, "b2c_register_import: len_each too small");
+  if (!c->ready) return fail(B2C_ESTATE, "b2c_register_import: comm not imported yet");
+  DeviceGuard g(c->device);
+  Registration r;
+  memset(&r, 0, sizeof(r));
+  r.local = (char*)ptr;
+  r.bytes = bytes;
+  for (int q = 0; q < c->world; ++q) {
+    RegBlob b;
+    memcpy(&b, (const char*)blobs + (size_t)q * len_each, sizeof(b));
+    if (b.magic != (B2C_MAGIC ^ 0x5a5a5a5au) || b.rank != q)
+      return fail(B2C_EINVAL, "b2c_register_import: blob %d is malformed or out of rank order", q);
+    if (b.bytes != bytes) return fail(B2C_EINVAL, "b2c_register_import: rank %d registered %llu bytes, we registered %zu", q, (unsigned long long)b.bytes, bytes);
+    if (q == c->rank) { r.peer[q] = (char*)ptr; continue; }
+    if (b.pid == (int64_t)getpid()) {
+      r.peer[q] = (char*)(uintptr_t)b.raw_ptr;  // same process: peer access was enabled at comm import
+    } else {
+      char* base = nullptr;
+      int rc = open_base(c, b.handle, &base);
+      if (rc) return rc;
+      r.peer[q] = base + b.offset;
+    }
+  }
+  if (c->nregs == c->regs_cap) {
+    c->regs_cap = c->regs_cap ? 2 * c->regs_cap : 16;
+    c->regs = (Registration*)realloc(c->regs, c->regs_cap * sizeof(Registration));
+  }
+  c->regs[c->nregs++] = r;
+  return B2C_OK;
+}
+
+extern "C" int b2c_deregister(b2c_comm* c, void* ptr) {
+  if (!c) return fail(B2C_EINVAL, "b2c_deregister: comm is NULL");
+  for (int i = 0; i < c->nregs; ++i)
+    if (c->regs[i].local == (char*)ptr) {
+      c->regs[i] = c->regs[--c->nregs];  // peer mappings stay open until destroy (shared per allocation)
+      return B2C_OK;
+    }
+  return fail(B2C_EINVAL, "b2c_deregister: %p is not registered", ptr);
+}
+
 // ---------------------------------------------------------------- knobs
 extern "C" int b2c_set_param(b2c_comm* c, int key, long v) {
   if (!c) return fail(B2C_EINVAL, "b2c_set_param: comm is NULL");
@@ -542,6 +738,10 @@ extern "C" int b2c_set_param(b2c_comm* c, int key, long v) {
     case B2C_PARAM_TWOSHOT_VARIANT:
       if (v != 0 && v != 1) return fail(B2C_EINVAL, "b2c_set_param: twoshot variant %ld (0 = push, 1 = pull)", v);
       break;
+    case B2C_PARAM_ZEROCOPY:
+      if (v != 0 && v != 1) return fail(B2C_EINVAL, "b2c_set_param: zerocopy=%ld (0 or 1)", v);
+      break;
+    case B2C_PARAM_ZEROCOPY_MIN_BYTES:
     case B2C_PARAM_CROSSOVER_BYTES:
       if (v < 0) return fail(B2C_EINVAL, "b2c_set_param: crossover=%ld", v);
       break;

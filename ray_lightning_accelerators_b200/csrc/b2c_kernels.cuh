@@ -493,3 +493,79 @@ __global__ void __launch_bounds__(32, 1) k_barrier(const __grid_constant__ B2cKA
   channel_barrier(a, c, c.epoch + 1u);
   epilogue(c);
 }
+
+// ================================================================= zero-copy two-shot allreduce
+// The caller's buffers themselves are peer-mapped (registered, or a local group), so there is
+// no staging pass and no copy-out:  barrier A (every rank's gradients are final: stream order
+// before its launch) -> rank r pulls shard r from all W buffers, reduces, and writes the result
+// back IN PLACE into all W buffers (only rank r ever touches shard r between the barriers)
+// -> barrier B.  HBM traffic per rank: S/W * W read-serves + S writes; NVLink 2(W-1)/W * S.
+// Needs 16-byte aligned buffers; the ragged tail (< one vector) is reduced element-wise by
+// rank 0 / channel 0.
+template <int MODE> struct Elem;
+template <> struct Elem<MODE_F32> {
+  static __device__ __forceinline__ float ld(const void* base, size_t e) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(static_cast<const float*>(base) + e));
+    return __uint_as_float(v);
+  }
+  static __device__ __forceinline__ void st(void* base, size_t e, float f) { static_cast<float*>(base)[e] = f; }
+};
+template <> struct Elem<MODE_BF16> {
+  static __device__ __forceinline__ float ld(const void* base, size_t e) {
+    unsigned short v;
+    asm volatile("ld.relaxed.sys.global.u16 %0, [%1];" : "=h"(v) : "l"(static_cast<const unsigned short*>(base) + e));
+    return __uint_as_float((uint32_t)v << 16);
+  }
+  static __device__ __forceinline__ void st(void* base, size_t e, float f) {
+    __nv_bfloat16 h = __float2bfloat16_rn(f);
+    static_cast<unsigned short*>(base)[e] = *reinterpret_cast<unsigned short*>(&h);
+  }
+};
+
+template <int MODE, int W>
+__global__ void __launch_bounds__(512, 1) k_allreduce_twoshot_zc(const __grid_constant__ B2cKArgs a) {
+  constexpr int VW = Mode<MODE>::VW;
+  constexpr int U = Unroll<W>::U;
+  Ctx c = prologue(a);
+  const size_t count = a.count;
+  const size_t nfull = count / VW;          // whole vectors
+  const size_t nvs = (nfull + W - 1) / W;   // vectors per shard
+  // in a local group every virtual rank shares one address space: buf[q] is rank q's buffer;
+  // in IPC mode buf[q] is rank q's buffer as mapped in THIS process.
+  channel_barrier(a, c, c.epoch + 1u);
+  if (!c.dead) {
+    const size_t s0 = (size_t)c.rank * nvs;
+    const size_t sl = (s0 >= nfull) ? 0 : ((s0 + nvs <= nfull) ? nvs : nfull - s0);
+    char* p[W];
+#pragma unroll
+    for (int q = 0; q < W; ++q) p[q] = static_cast<char*>(a.buf[q]) + s0 * 16;
+    B2C_FOR_OWNED(sl, U, {
+      uint4 v[U][W];
+      _Pragma("unroll") for (int u = 0; u < U; ++u)
+        _Pragma("unroll") for (int q = 0; q < W; ++q)
+          if (pred[u]) v[u][q] = ld_sys_v4(p[q] + idx[u] * 16);
+      _Pragma("unroll") for (int u = 0; u < U; ++u) if (pred[u]) {
+        Acc<MODE> acc; acc.init(v[u][0], a.scale);
+        _Pragma("unroll") for (int q = 1; q < W; ++q) acc.add(v[u][q], a.scale);
+        const uint4 res = acc.finish();
+        _Pragma("unroll") for (int k = 0; k < W; ++k) {  // own copy first, then peers rotated
+          int q = c.rank + k; if (q >= W) q -= W;
+          st_v4(static_cast<char*>(a.buf[q]) + (s0 + idx[u]) * 16, res);
+        }
+      }
+    })
+    if (c.rank == 0 && c.b == 0) {
+      const size_t e = nfull * VW + threadIdx.x;
+      if (e < count) {
+        float acc = __fmul_rn(Elem<MODE>::ld(a.buf[0], e), a.scale);
+#pragma unroll
+        for (int q = 1; q < W; ++q) acc = __fadd_rn(acc, __fmul_rn(Elem<MODE>::ld(a.buf[q], e), a.scale));
+#pragma unroll
+        for (int q = 0; q < W; ++q) Elem<MODE>::st(a.buf[q], e, acc);
+      }
+    }
+  }
+  channel_barrier(a, c, c.epoch + 2u);
+  epilogue(c);
+}

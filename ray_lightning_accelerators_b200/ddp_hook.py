@@ -20,8 +20,11 @@ from .comm import ALGO_AUTO, Comm
 class B2cHookState:
     """State object handed to DDP.register_comm_hook (the `state` of hook(state, bucket))."""
 
-    def __init__(self, comm, wire_dtype=None, algo=ALGO_AUTO):
+    def __init__(self, comm, wire_dtype=None, algo=ALGO_AUTO, register_buckets=True):
         self.comm = comm
+        # first time a bucket buffer is seen it is registered with every peer (collective, on the
+        # autograd thread, control-plane bytes only) so later steps reduce it in place
+        self.register_buckets = register_buckets and wire_dtype is None
         self.wire_dtype = wire_dtype
         self.algo = algo
         # high-priority side stream: the reduce of bucket k overlaps the rest of backward
@@ -44,6 +47,8 @@ def allreduce_hook(state, bucket):
     buf = bucket.buffer()
     comm = state.comm
     wire = state.wire_dtype if (state.wire_dtype is not None and buf.dtype == torch.float32) else None
+    if state.register_buckets:
+        comm.register(buf)  # no-op after the first step (cached by pointer)
     state.stream.wait_stream(torch.cuda.current_stream(buf.device))
     with torch.cuda.stream(state.stream):
         if state.timing is not None:

@@ -17,7 +17,15 @@ from oracle import oracle as O  # noqa: E402
 from ray_lightning_accelerators_b200 import _lib, ddp_hook  # noqa: E402
 from ray_lightning_accelerators_b200.comm import ALGO_ONESHOT, ALGO_TWOSHOT, Comm  # noqa: E402
 
-ALGOS = [(ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1)]
+# variant 0 / 1: staged two-shot (push / pull); 2: zero-copy two-shot on a registered buffer
+ALGOS = [(ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1), (ALGO_TWOSHOT, 2)]
+
+
+def select(comm, variant, t=None):
+    comm.set_param(_lib.PARAM_ZEROCOPY, 1 if variant == 2 else 0)
+    comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant if variant < 2 else 0)
+    if variant == 2 and t is not None:
+        assert comm.register(t), "cudaMalloc-backed torch memory must be registrable"
 
 
 def bits(t):
@@ -46,9 +54,11 @@ def main():
             ref = torch.from_numpy(grads[rank]).to(dev).div_(world)
             dist.all_reduce(ref)
             for algo, variant in ALGOS:
-                comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
                 t = torch.from_numpy(grads[rank]).to(dev)
+                select(comm, variant, t)
+                z0 = comm.stats()["zerocopy_launches"]
                 comm.allreduce(t, algo=algo)
+                assert (comm.stats()["zerocopy_launches"] > z0) == (variant == 2), "wrong path taken"
                 torch.cuda.synchronize()
                 comm.check_alive()
                 got = t.cpu().numpy()
@@ -63,8 +73,8 @@ def main():
         gb = [O.to_bf16_bits(O.payload("randn", n, r)) for r in range(world)]
         want = O.b2c_allreduce_bf16(gb)
         for algo, variant in ALGOS:
-            comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
             t = torch.from_numpy(gb[rank].view(np.int16).copy()).to(dev).view(torch.bfloat16)
+            select(comm, variant, t)
             comm.allreduce(t, algo=algo)
             torch.cuda.synchronize()
             assert np.array_equal(t.view(torch.int16).cpu().numpy().view(np.uint16), want), ("bf16", n, algo)
@@ -89,10 +99,10 @@ def main():
     # ---- stress: 200 back-to-back calls, payload changes every call, no host sync
     outs = []
     for i in range(200):
-        algo, variant = ALGOS[i % 3]
-        comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
+        algo, variant = ALGOS[i % 4]
         n = 1000 + 997 * (i % 50)
         t = torch.full((n,), float(rank + i), device=dev)
+        select(comm, variant, t)
         comm.allreduce(t, algo=algo)
         outs.append((t, sum(r + i for r in range(world)) / world))
     torch.cuda.synchronize()
@@ -100,6 +110,8 @@ def main():
     for t, want in outs:
         assert torch.allclose(t, torch.full_like(t, want), rtol=1e-6, atol=0), "stress"
 
+    comm.set_param(_lib.PARAM_ZEROCOPY, 1)
+    comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, 0)
     # ---- DDP: our hook vs stock NCCL DDP, MLP (config #2) 100 steps, loss within 1e-5 relative
     def train(use_b2c):
         model = workloads.build_model("mnist_mlp", seed=0).to(dev)

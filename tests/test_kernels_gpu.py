@@ -26,8 +26,14 @@ else:  # collected on CPU boxes, skipped by the marker
     ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT = 0, 1, 2
 
 DEV = "cuda:0"
-ALGOS = [(ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1)]
-ALGO_IDS = ["oneshot", "twoshot-push", "twoshot-pull"]
+# (algo, variant): variant 0 / 1 = staged two-shot (push / pull), 2 = zero-copy two-shot in place
+ALGOS = [(ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1), (ALGO_TWOSHOT, 2)]
+ALGO_IDS = ["oneshot", "twoshot-push", "twoshot-pull", "twoshot-zerocopy"]
+
+
+def _select(group, variant):
+    group.set_param(_lib.PARAM_ZEROCOPY, 1 if variant == 2 else 0)
+    group.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant if variant < 2 else 0)
 
 
 @pytest.fixture(scope="module")
@@ -50,7 +56,7 @@ def groups():
 
 def _run(group, arrs, algo, variant, wire=None, scale=None, dtype=torch.float32, offset=0):
     """arrs: per-rank numpy fp32 (or uint16 bf16 bits).  Returns per-rank numpy outputs."""
-    group.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
+    _select(group, variant)
     ts = []
     for a in arrs:
         if dtype == torch.bfloat16:
@@ -249,8 +255,8 @@ def test_back_to_back_calls_change_payload_every_time(groups):
     sizes = [int(s) for s in rng.integers(1, 300000, size=60)]
     todo = []
     for i, n in enumerate(sizes):
-        algo, variant = ALGOS[i % 3]
-        g.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
+        algo, variant = ALGOS[i % 4]
+        _select(g, variant)
         grads = [O.payload("randn", n, r, seed=100 * i) for r in range(world)]
         ts = [torch.from_numpy(x).to(DEV, non_blocking=False) for x in grads]
         g.allreduce(ts, algo=algo)
@@ -322,7 +328,7 @@ def test_full_size_buckets_properties(groups, world):
         for x in grads[1:]:
             want = want + x * s
         for algo, variant in ALGOS:
-            g.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
+            _select(g, variant)
             ts = [x.clone() for x in grads]
             g.allreduce(ts, algo=algo)
             torch.cuda.synchronize()

@@ -19,6 +19,8 @@ def hbm_bytes(algo, variant, W, S):
         return 2 * S
     if algo == ALGO_ONESHOT:
         return W * (2 * S + W * S + S)  # stage r+w, read W copies, write result
+    if variant == 2:
+        return W * 2 * S  # zero-copy: each rank reads W shards (S) and writes W shards (S), in place
     per = 2 * S + S + S / W  # stage r+w, reduce-scatter read of W shards, own shard -> buf
     if variant == 0:
         per += (W - 1) * S / W + 2 * (W - 1) * S / W  # push to peers, gather local arena -> buf
@@ -43,12 +45,13 @@ def main():
             for S in sizes:
                 n = S // (4 if dtype == torch.float32 else 2)
                 ts = [torch.randn(n, device="cuda").to(dtype) for _ in range(W)]
-                for algo, variant in ((ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1)):
+                for algo, variant in ((ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1), (ALGO_TWOSHOT, 2)):
                     if W == 1 and algo != ALGO_ONESHOT:
                         continue
                     if algo == ALGO_ONESHOT and W * S > (512 << 20):
                         continue
-                    g.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
+                    g.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant if variant < 2 else 0)
+                    g.set_param(_lib.PARAM_ZEROCOPY, 1 if variant == 2 else 0)
                     for _ in range(3):
                         g.allreduce(ts, algo=algo)
                     torch.cuda.synchronize()

@@ -52,7 +52,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--max-bytes", type=int, default=1 << 30)
     ap.add_argument("--quick", action="store_true")
-    ap.add_argument("--blocks", default="16,32,64,128")
+    ap.add_argument("--blocks", default="32,64,128")
     args = ap.parse_args()
 
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -87,7 +87,7 @@ def main():
             if rank == 0:
                 print(rows[-1], flush=True)
             configs = []
-            for algo, variant in ((ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1)):
+            for algo, variant in ((ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1), (ALGO_TWOSHOT, 2)):
                 if algo == ALGO_ONESHOT and S > (64 << 20):
                     continue
                 for nb in block_opts:
@@ -95,11 +95,14 @@ def main():
                         continue  # geometry clamps tiny messages to a few channels anyway
                     configs.append((algo, variant, nb))
             for algo, variant, nb in configs:
-                comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant)
+                comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, variant if variant < 2 else 0)
+                comm.set_param(_lib.PARAM_ZEROCOPY, 1 if variant == 2 else 0)  # 2 = in place on registered buffers
                 comm.set_param(_lib.PARAM_MAX_BLOCKS_ONESHOT, nb)
                 comm.set_param(_lib.PARAM_MAX_BLOCKS_TWOSHOT, nb)
                 # parity first (same run): vs NCCL and bitwise across replicas
                 y = x.clone()
+                if variant == 2:
+                    comm.register(y)
                 comm.allreduce(y, algo=algo)
                 torch.cuda.synchronize()
                 comm.check_alive()
@@ -114,6 +117,8 @@ def main():
                 bitexact = bool(torch.equal(y.view(torch.int16 if es == 2 else torch.int32),
                                             ref.view(torch.int16 if es == 2 else torch.int32)))
                 buf = x.clone()
+                if variant == 2:
+                    comm.register(buf)
 
                 def b2c_fn():
                     comm.allreduce(buf, algo=algo)
@@ -121,7 +126,8 @@ def main():
                 med, p99, mean = timed(b2c_fn, comm, flush, args.iters, args.warmup)
                 st = comm.stats()
                 rows.append(dict(impl="b2c", W=world, dtype=str(dtype).split(".")[1], bytes=S,
-                                 algo={1: "oneshot", 2: "twoshot"}[algo], variant=variant, max_blocks=nb,
+                                 algo={1: "oneshot", 2: "twoshot"}[algo], variant=variant, zerocopy=(variant == 2),
+                                 max_blocks=nb,
                                  blocks=st["last_blocks"], us_med=med, us_p99=p99, us_mean=mean,
                                  busbw_GBps=busf / med / 1e3, rel_err_vs_nccl=err, within_tol=bool(err <= tol),
                                  bitexact_vs_nccl=bitexact, replicas_identical=same))
