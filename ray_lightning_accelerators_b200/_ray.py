@@ -3,7 +3,8 @@
 The reference launches its workers as Ray actors (ray_lightning/ray_ddp.py:17-31,92-97) and
 moves the trainer / results through the Ray object store.  Ray is not installed in this image
 and cannot be, so this module provides the SUBSET of the `ray` API the reference touches,
-implemented with spawned local processes: remote actor classes with .options(num_cpus,
+implemented with local worker processes (plain `python -m ..._actor_main` children, so the
+user's script is never re-imported and needs no __main__ guard): remote actor classes with .options(num_cpus,
 num_gpus).remote(), method.remote() futures, get / wait / put / kill, and a queue actor.
 This module is the single seam where the real `ray` would plug in; nothing else in the package
 imports ray.
@@ -13,15 +14,17 @@ child BEFORE torch is imported, so the worker's device index is 0 (the pinning c
 ray_lightning/tests/test_ddp_gpu.py:83-103).
 """
 import itertools
-import multiprocessing as mp
 import os
-import queue as _queue
+import secrets
+import subprocess
+import sys
+import tempfile
 import threading
-import traceback
+import time
+from multiprocessing.connection import Client
 
 import cloudpickle
 
-_ctx = mp.get_context("spawn")
 _ids = itertools.count()
 
 
@@ -126,33 +129,7 @@ def _release_gpu(g):
             _gpu_free.sort()
 
 
-# ------------------------------------------------------------------ actor process
-def _actor_main(conn, cls_payload, init_payload, env):
-    os.environ.update(env)
-    try:
-        cls = cloudpickle.loads(cls_payload)
-        args, kwargs = cloudpickle.loads(init_payload)
-        obj = cls(*args, **kwargs)
-        conn.send((-1, True, None))
-    except BaseException:
-        conn.send((-1, False, traceback.format_exc()))
-        return
-    while True:
-        try:
-            msg = conn.recv()
-        except EOFError:
-            return
-        if msg is None:
-            return
-        call_id, name, payload = msg
-        try:
-            args, kwargs = cloudpickle.loads(payload)
-            out = getattr(obj, name)(*args, **kwargs)
-            conn.send((call_id, True, cloudpickle.dumps(out)))
-        except BaseException:
-            conn.send((call_id, False, traceback.format_exc()))
-
-
+# ------------------------------------------------------------------ actor handles
 class _Method:
     def __init__(self, handle, name):
         self._h, self._name = handle, name
@@ -161,40 +138,72 @@ class _Method:
         return self._h._call(self._name, args, kwargs)
 
 
+def _connect(address, authkey, proc=None, timeout=120.0):
+    deadline = time.monotonic() + timeout
+    while True:
+        try:
+            return Client(address, family="AF_UNIX", authkey=authkey)
+        except (FileNotFoundError, ConnectionRefusedError):
+            if proc is not None and proc.poll() is not None:
+                raise RayActorError(f"actor process exited with code {proc.returncode} before it was reachable")
+            if time.monotonic() > deadline:
+                raise RayActorError("timed out connecting to the actor process")
+            time.sleep(0.01)
+
+
 class ActorHandle:
-    def __init__(self, cls, args, kwargs, options):
-        self._options = dict(options)
+    """Client side of one actor.  The creating handle owns the process; a pickled copy that
+    travels to another process reconnects to the same actor (Ray handle semantics)."""
+
+    def __init__(self, cls=None, args=(), kwargs=None, options=None, _attach=None):
+        self._options = dict(options or {})
         self._gpu = None
-        env = {}
+        self._proc = None
+        self._boot = None
+        self._pending = {}
+        self._lock = threading.Lock()
+        if _attach is not None:
+            self._address, self._authkey = _attach
+            self._conn = _connect(self._address, self._authkey)
+            self._start_reader()
+            return
+        env = dict(os.environ)
         if int(self._options.get("num_gpus", 0) or 0) >= 1:
             self._gpu = _acquire_gpu()
             env["CUDA_VISIBLE_DEVICES"] = self._gpu
         ncpu = self._options.get("num_cpus", None)
         if ncpu:  # Ray exports OMP_NUM_THREADS=num_cpus for actors that reserve CPUs
             env["OMP_NUM_THREADS"] = str(max(1, int(ncpu)))
-        self._conn, child = _ctx.Pipe()
-        self._proc = _ctx.Process(target=_actor_main, daemon=True,
-                                  args=(child, cloudpickle.dumps(cls), cloudpickle.dumps((args, kwargs)), env))
-        self._proc.start()
-        child.close()
-        self._pending = {}
-        self._lock = threading.Lock()
-        self._alive = True
-        boot = _Future(self)
-        self._pending[-1] = boot
-        self._reader = threading.Thread(target=self._read_loop, daemon=True)
-        self._reader.start()
+        self._authkey = secrets.token_bytes(16)
+        self._address = os.path.join(tempfile.gettempdir(), f"b2c-actor-{os.getpid()}-{next(_ids)}-{secrets.token_hex(4)}.sock")
+        pkg_root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        env["PYTHONPATH"] = pkg_root + os.pathsep + env.get("PYTHONPATH", "")
+        self._proc = subprocess.Popen([sys.executable, "-m", "ray_lightning_accelerators_b200._actor_main",
+                                       self._address, self._authkey.hex()], env=env)
         try:
-            boot.result()
+            self._conn = _connect(self._address, self._authkey, self._proc)
+            self._start_reader()
+            # boot is asynchronous so that several actors start (import torch ...) in parallel;
+            # the first method call waits for it and re-raises a constructor failure
+            self._boot = self._send(("__init__", None, cloudpickle.dumps(cls), cloudpickle.dumps((args, kwargs or {})),
+                                     list(sys.path)))
         except BaseException:
             self._shutdown()
             raise
+
+    def __reduce__(self):
+        return (_attach_handle, (self._address, self._authkey, self._options))
+
+    def _start_reader(self):
+        self._alive = True
+        self._reader = threading.Thread(target=self._read_loop, daemon=True)
+        self._reader.start()
 
     def _read_loop(self):
         while True:
             try:
                 call_id, ok, payload = self._conn.recv()
-            except (EOFError, OSError):
+            except (EOFError, OSError, TypeError):
                 break
             with self._lock:
                 fut = self._pending.pop(call_id, None)
@@ -210,15 +219,27 @@ class ActorHandle:
         for fut in pending.values():
             fut._set(False, RayActorError("actor died before the call returned"))
 
-    def _call(self, name, args, kwargs):
+    def _send(self, msg):
+        """msg = (kind, None, ...): slot 1 is replaced by the call id."""
         if not self._alive:
             raise RayActorError("actor is dead")
         fut = _Future(self)
         call_id = next(_ids)
         with self._lock:
             self._pending[call_id] = fut
-        self._conn.send((call_id, name, cloudpickle.dumps((args, kwargs))))
+            self._conn.send((msg[0], call_id) + tuple(msg[2:]))
         return fut
+
+    def _call(self, name, args, kwargs):
+        boot = getattr(self, "_boot", None)
+        if boot is not None:
+            try:
+                boot.result()
+            except BaseException:
+                self._shutdown()
+                raise
+            self._boot = None
+        return self._send(("call", None, name, cloudpickle.dumps((args, kwargs))))
 
     def __getattr__(self, name):
         if name.startswith("_"):
@@ -229,16 +250,21 @@ class ActorHandle:
         if self._proc is None:
             return
         try:
-            self._conn.send(None)
+            self._send(("__exit__", None)).result(timeout=5)
         except Exception:
             pass
-        self._proc.join(timeout=5)
-        if self._proc.is_alive():
-            self._proc.terminate()
-            self._proc.join(timeout=5)
+        try:
+            self._proc.wait(timeout=5)
+        except Exception:
+            self._proc.kill()
+            self._proc.wait(timeout=5)
         try:
             self._conn.close()
         except Exception:
+            pass
+        try:
+            os.unlink(self._address)
+        except OSError:
             pass
         _release_gpu(self._gpu)
         self._gpu = None
@@ -246,7 +272,11 @@ class ActorHandle:
         self._proc = None
 
     def _is_alive(self):
-        return self._proc is not None and self._proc.is_alive()
+        return self._proc is not None and self._proc.poll() is None
+
+
+def _attach_handle(address, authkey, options):
+    return ActorHandle(options=options, _attach=(address, authkey))
 
 
 class ActorClass:
@@ -289,50 +319,75 @@ def get_node_ip_address():
 
 
 # ------------------------------------------------------------------ queue actor
-_manager = None
-
-
 class Empty(Exception):
     pass
 
 
-class Queue:
-    """The part of ray.util.queue.Queue the reference uses (util.py:71-93): put / get / empty /
-    shutdown, picklable so it can be shipped to the workers."""
+class _QueueActor:
+    """Lives in its own actor process (the reference's Queue wraps such an actor,
+    util.py:17-85); items are opaque cloudpickled bytes."""
 
-    def __init__(self, maxsize=0, actor_options=None):
-        global _manager
-        if _manager is None:
-            _manager = _ctx.Manager()
+    def __init__(self, maxsize):
+        import collections
         self.maxsize = maxsize
-        self._q = _manager.Queue(maxsize)
-
-    def put(self, item, block=True, timeout=None):
-        self._q.put(cloudpickle.dumps(item), block, timeout)
-
-    def get(self, block=True, timeout=None):
-        try:
-            return cloudpickle.loads(self._q.get(block, timeout))
-        except _queue.Empty:
-            raise Empty
-
-    def empty(self):
-        return self._q.empty()
+        self.items = collections.deque()
 
     def qsize(self):
-        return self._q.qsize()
+        return len(self.items)
+
+    def put_nowait(self, item):
+        if self.maxsize > 0 and len(self.items) >= self.maxsize:
+            return False
+        self.items.append(item)
+        return True
+
+    def get_nowait(self):
+        if not self.items:
+            return (False, None)
+        return (True, self.items.popleft())
+
+
+class Queue:
+    """The part of ray.util.queue.Queue the reference uses (util.py:71-93): put / get / empty /
+    qsize / shutdown.  Picklable: the copy shipped to a worker talks to the same actor."""
+
+    def __init__(self, maxsize=0, actor_options=None):
+        self.maxsize = maxsize
+        self.actor = ActorClass(_QueueActor, actor_options or {}).remote(maxsize)
+
+    def put(self, item, block=True, timeout=None):
+        payload = cloudpickle.dumps(item)
+        deadline = None if timeout is None else time.monotonic() + timeout
+        while not get(self.actor.put_nowait.remote(payload)):
+            if not block or (deadline is not None and time.monotonic() > deadline):
+                raise RuntimeError("queue full")
+            time.sleep(0.005)
+
+    def get(self, block=True, timeout=None):
+        deadline = None if timeout is None else time.monotonic() + timeout
+        while True:
+            ok, payload = get(self.actor.get_nowait.remote())
+            if ok:
+                return cloudpickle.loads(payload)
+            if not block or (deadline is not None and time.monotonic() > deadline):
+                raise Empty
+            time.sleep(0.005)
+
+    def empty(self):
+        return get(self.actor.qsize.remote()) == 0
+
+    def qsize(self):
+        return get(self.actor.qsize.remote())
 
     def shutdown(self):
-        self._q = None
+        if self.actor is not None and self.actor._proc is not None:
+            kill(self.actor)
+        self.actor = None
 
 
 def shutdown():
-    global _manager
     for a in list(_live_actors):
         kill(a)
-    if _manager is not None:
-        _manager.shutdown()
-        _manager = None
 
 
 def is_real_ray():
