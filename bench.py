@@ -1,0 +1,400 @@
+#!/usr/bin/env python
+"""bench.py — BASELINE.json's metric on BASELINE.json's config.
+
+metric  : train samples/sec (ResNet-50, synthetic 224x224, batch 256 per GPU, fp32 DDP with 25 MB
+          buckets through RayAccelerator's worker-side plugin methods), plus the gradient-allreduce
+          bus bandwidth of the b2c kernels on that model's real bucket sizes.
+launch  : python bench.py --gpus 1 ...            (single process)
+          python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+                 --master-port P bench.py --gpus N --steps K --warmup W      (one rank per GPU)
+arms    : default          = this repo (libb2c.so kernels on the gradient path; fails loudly without it)
+          --impl reference = the reference's own CPU path: RayAccelerator(use_gpu=False) => stock torch
+                             DDP over gloo on the host cores (oracle/gloo_ref.py), bounded sample.
+One JSON line on stdout from rank 0.  Timing: CUDA events, barrier + synchronize on both sides, max
+over ranks; every timed step touches far more than the 126 MB L2 (activations of a 256-image batch).
+"""
+import argparse
+import json
+import os
+import socket
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+NVLINK_NOMINAL_GBPS = 900.0      # per direction per GPU (BASELINE.json)
+NVLINK_MEASURED_COPY_GBPS = 770.0  # peer copy on this pool (B200_PROFILING.md)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region (recipe's clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------- reference arm (CPU)
+def run_reference(args):
+    """The reference's own CPU path for this workload: W = --gpus workers, gloo, stock DDP, every
+    host thread it can use (ray_ddp.py:92-97 gives each actor num_cpus_per_worker CPUs)."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return  # under torchrun only rank 0 works; the other ranks exit 0
+    from oracle import gloo_ref
+    cores = os.cpu_count() or 1
+    world = max(1, args.gpus)
+    threads = max(1, cores // world)
+    batch = args.ref_batch
+    steps = max(1, min(args.steps, args.ref_max_steps))
+    warmup = max(1, min(args.warmup, 2))
+    r = gloo_ref.run_ddp(world, args.model, steps=steps, batch=batch, warmup=warmup, threads=threads,
+                         distinct_batches=2, find_unused=True)
+    sps = r["samples_per_sec"]
+    sample = (f"{args.model} fp32, stock torch DDP over gloo, {world} worker(s) x {threads} thread(s), "
+              f"batch {batch}/worker (bounded sample of the 256/GPU workload), {steps} timed steps")
+    line = {
+        "impl": "reference", "metric": "train_samples_per_sec", "value": sps, "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": r["seconds"] / steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.model} synthetic 224x224 DDP (BASELINE configs[2]); CPU arm uses batch {batch}/worker",
+                   "global_batch": batch * world, "parallelism": f"dp{world}", "backend": "gloo"},
+        "cpu_baseline": {"value": sps, "unit": "samples/s", "cores": threads * world, "kind": "reference",
+                         "sample": sample, "host_cores": cores},
+        "e2e": {"value": sps, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------- b2c arm (GPU)
+def _build_worker(args, rank, world, local):
+    """Worker set-up through the reference-facing plugin: the same RayAccelerator methods a Ray actor
+    runs inside train_remote (ray_ddp.py:199-267), in the order PTL's ddp_train calls them."""
+    import torch
+    from examples import workloads
+    from ray_lightning_accelerators_b200 import RayAccelerator
+    from ray_lightning_accelerators_b200.mini_pl import Trainer
+
+    acc = RayAccelerator(num_workers=world, num_cpus_per_worker=1, use_gpu=True)
+    trainer = Trainer(gpus=1, accelerator=acc, checkpoint_callback=False)
+    acc.trainer = trainer
+    acc.global_rank = rank
+    acc.global_to_local = list(range(world)) if torch.cuda.device_count() > 1 else [0] * world
+    addr = os.environ.get("MASTER_ADDR", "127.0.0.1")
+    port = os.environ.get("MASTER_PORT") or str(_free_port())
+    acc.ddp_address = f"tcp://{addr}:{port}"
+    acc.set_world_ranks(rank)
+    acc.init_ddp_connection(rank, world)          # process group + b2c communicator (IPC handles)
+    acc.init_device(rank, is_master=(rank == 0))
+    model = workloads.build_model(args.model, seed=0)
+    acc.model_to_device(model)
+    opt = model.configure_optimizers()
+    ddp = _wrap(acc, model, args)
+    return acc, model, ddp, opt
+
+
+class _Plain(object):
+    pass
+
+
+def _wrap(acc, model, args):
+    """configure_ddp, but wrapping the bare module: the bench calls forward(x) directly."""
+    import torch
+    from ray_lightning_accelerators_b200.ddp_hook import wrap_ddp
+    wire = torch.bfloat16 if args.wire == "bf16" else None
+    return wrap_ddp(model, acc.b2c_comm, device_ids=acc.get_device_ids(), wire_dtype=wire,
+                    find_unused_parameters=True)
+
+
+def _bucket_stats(state):
+    """Per-launch device times recorded by the hook around every b2c_allreduce of the timed region."""
+    import torch
+    torch.cuda.synchronize()
+    by_size = {}
+    for e0, e1, nbytes in state.timing:
+        by_size.setdefault(nbytes, []).append(e0.elapsed_time(e1) * 1e3)
+    return {nb: sum(v) / len(v) for nb, v in by_size.items()}, sum(len(v) for v in by_size.values())
+
+
+def run_b2c(args):
+    import torch
+    import torch.distributed as dist
+    from examples import workloads
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 with torch.distributed.run")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (b2c arm) needs a CUDA device; there is no CPU fallback. "
+                         "Use --impl reference for the reference's CPU path.")
+    torch.backends.cudnn.benchmark = True
+    acc, model, ddp, opt = _build_worker(args, rank, world, local)
+    comm, state = acc.b2c_comm, ddp._b2c_state
+    dev = torch.device("cuda", torch.cuda.current_device())
+    batch = args.batch
+    K, W = args.steps, max(3, args.warmup)
+
+    # ---- leg 1 ("value"): inputs already resident in HBM when the timed region starts
+    x_dev, y_dev = [t.to(dev) for t in workloads.synthetic_batch(args.model, batch, rank, 0)]
+
+    def step(x, y):
+        opt.zero_grad(set_to_none=True)
+        loss = model.loss_fn(ddp(x), y)
+        loss.backward()
+        opt.step()
+        return loss
+
+    for _ in range(W):
+        step(x_dev, y_dev)
+    torch.cuda.synchronize()
+    dist.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    state.enable_timing()
+    launches0 = comm.stats()["launches"]
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step(x_dev, y_dev)
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = comm.stats()["launches"] - launches0
+    per_bucket_us, n_timed = _bucket_stats(state)
+    state.timing = None
+    ms_total = float(ms.item())
+    value = world * batch * K / (ms_total / 1e3)
+
+    # ---- leg 2 ("e2e"): host buffers; H2D of the step's batch from pinned memory and a D2H read of
+    # the loss inside the timed region, every step
+    host = [workloads.synthetic_batch(args.model, batch, rank, s) for s in range(2)]
+    host = [(x.pin_memory(), y.pin_memory()) for x, y in host]
+    h2d = host[0][0].numel() * host[0][0].element_size() + host[0][1].numel() * host[0][1].element_size()
+
+    def e2e_step(s):
+        xh, yh = host[s % 2]
+        x = xh.to(dev, non_blocking=True)
+        y = yh.to(dev, non_blocking=True)
+        return float(step(x, y).item())  # device -> host read of the result, every step
+
+    for s in range(2):
+        e2e_step(s)
+    torch.cuda.synchronize()
+    dist.barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    last = None
+    for s in range(K):
+        last = e2e_step(s)
+    f1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms2 = torch.tensor([f0.elapsed_time(f1)], device=dev, dtype=torch.float64)
+    dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
+    e2e_value = world * batch * K / (float(ms2.item()) / 1e3)
+
+    # ---- roofline of the dominant b2c kernel of the timed region (largest share of our device time)
+    peaks, peak_kind = _peaks()
+    total_us = {nb: us * 1.0 for nb, us in per_bucket_us.items()}
+    dom = max(total_us, key=lambda nb: total_us[nb]) if total_us else None
+    roofline = None
+    if dom is not None:
+        us = per_bucket_us[dom]
+        if world == 1:
+            alg = 2.0 * dom  # read S, write S (W = 1: scale pass in place)
+            roofline = {"bound": "hbm", "kernel": "k_allreduce_oneshot<f32,W=1>", "achieved": alg / us / 1e3,
+                        "peak": peaks["hbm_gbs"], "peak_kind": f"{peak_kind} HBM copy", "unit": "GB/s",
+                        "frac": alg / us / 1e3 / peaks["hbm_gbs"], "traffic": None,
+                        "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom}
+        else:
+            alg = 2.0 * (world - 1) / world * dom  # NVLink bytes per GPU per direction (busbw numerator)
+            roofline = {"bound": "nvlink", "kernel": f"k_allreduce_twoshot_zc<f32,W={world}>",
+                        "achieved": alg / us / 1e3, "peak": NVLINK_NOMINAL_GBPS,
+                        "peak_kind": "nominal NVLink 5 per direction (measured peer copy 770 GB/s)", "unit": "GB/s",
+                        "frac": alg / us / 1e3 / NVLINK_NOMINAL_GBPS,
+                        "frac_of_measured_copy": alg / us / 1e3 / NVLINK_MEASURED_COPY_GBPS, "traffic": None,
+                        "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom}
+    buckets = [{"bytes": nb, "us": per_bucket_us[nb],
+                "busbw_GBps": (2.0 * (world - 1) / world * nb / per_bucket_us[nb] / 1e3) if world > 1 else None}
+               for nb in sorted(per_bucket_us)]
+
+    allreduce = _allreduce_section(args, comm, rank, world, dev)
+    cpu_baseline = _cpu_baseline(args) if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
+
+    if rank == 0:
+        line = {
+            "metric": "train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32" if args.wire != "bf16" else "f32 grads on a bf16 wire",
+            "data": "synthetic",
+            "config": {"workload": f"{args.model} synthetic 224x224, batch {batch}/GPU, SGD momentum, torch DDP 25 MB "
+                                   f"buckets via RayAccelerator(use_gpu=True) plugin methods (BASELINE configs[2])",
+                       "global_batch": batch * world, "parallelism": f"dp{world}",
+                       "l2": "inputs larger than L2 (activations of a 256-image batch >> 126 MB); no flush needed",
+                       "grad_path": "libb2c.so: zero-copy two-shot on registered DDP buckets" if world > 1
+                                    else "libb2c.so: W=1 scale pass (no peer)"},
+            "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                    "ms_per_step": float(ms2.item()) / K, "last_loss": last},
+            "gpu_launches": int(launches), "b2c_launches_timed": int(n_timed),
+            "clocks": clocks, "roofline": roofline, "grad_buckets": buckets, "allreduce": allreduce,
+        }
+        if cpu_baseline is not None:
+            line["cpu_baseline"] = cpu_baseline
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    from ray_lightning_accelerators_b200.ray_ddp import _close_worker_comm
+    _close_worker_comm()
+    dist.destroy_process_group()
+
+
+RESNET50_BUCKETS = [12415000, 31500000, 29664000, 27021000, 1625000]  # bytes, launch order
+
+
+def _allreduce_section(args, comm, rank, world, dev):
+    """The second half of BASELINE.json's metric: gradient-allreduce bus GB/s on the real bucket sizes.
+    N>1: over NVLink, b2c vs stock NCCL in the same processes.  N=1: there is no link; the same kernels
+    run as 8 virtual ranks on the one GPU (HBM-bound), reported against the measured HBM peak."""
+    import torch
+    import torch.distributed as dist
+    from ray_lightning_accelerators_b200 import _lib
+    from ray_lightning_accelerators_b200.comm import ALGO_AUTO, ALGO_TWOSHOT, LocalGroup
+    iters = args.ar_iters
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    out = []
+    peaks, peak_kind = _peaks()
+
+    def timed(fn, barrier):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(iters):
+            flush.fill_(1)               # L2 flush between timed launches
+            torch.cuda._sleep(200000)    # keep the GPU busy so the host runs ahead of the stream
+            barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record(); b.synchronize()
+            ts.append(a.elapsed_time(b) * 1e3)
+        t = torch.tensor(ts, device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.sort().values[len(ts) // 2])
+
+    if world > 1:
+        for S in RESNET50_BUCKETS:
+            x = torch.randn(S // 4, device=dev)
+            comm.register(x)
+            us = timed(lambda: comm.allreduce(x, algo=ALGO_AUTO), comm.barrier)
+            y = torch.randn(S // 4, device=dev)
+            us_nccl = timed(lambda: dist.all_reduce(y), comm.barrier)
+            bus = 2.0 * (world - 1) / world * S
+            out.append({"bytes": S, "us": us, "busbw_GBps": bus / us / 1e3, "frac_of_900": bus / us / 1e3 / NVLINK_NOMINAL_GBPS,
+                        "nccl_us": us_nccl, "nccl_busbw_GBps": bus / us_nccl / 1e3})
+        return {"mode": f"nvlink W={world}", "timing": "median of %d, L2 flushed, max over ranks" % iters, "buckets": out}
+    g = LocalGroup(8, device=dev.index or 0, arena_bytes=8 << 20)
+    g.set_param(_lib.PARAM_TIMEOUT_MS, 3000)
+    for S in RESNET50_BUCKETS:
+        ts = [torch.randn(S // 4, device=dev) for _ in range(8)]
+        us = timed(lambda: g.allreduce(ts, algo=ALGO_TWOSHOT), lambda: None)
+        alg = 2.0 * 8 * S  # every virtual rank reads S and writes S (zero-copy two-shot, in place)
+        out.append({"bytes": S, "us": us, "hbm_GBps": alg / us / 1e3, "frac_of_hbm_peak": alg / us / 1e3 / peaks["hbm_gbs"]})
+    g.close()
+    return {"mode": "one GPU, 8 virtual ranks (HBM-bound emulation, no NVLink at N=1)", "peak": peaks["hbm_gbs"],
+            "peak_kind": f"{peak_kind} HBM copy GB/s", "timing": "median of %d, L2 flushed" % iters, "buckets": out}
+
+
+def _cpu_baseline(args):
+    """The reference's CPU path on this box's host cores, bounded sample (~10-30 s of CPU work):
+    2 gloo workers (config #1's worker count) sharing all cores."""
+    from oracle import gloo_ref
+    cores = os.cpu_count() or 1
+    world = 2
+    threads = max(1, cores // world)
+    r = gloo_ref.run_ddp(world, args.model, steps=2, batch=args.ref_batch, warmup=1, threads=threads, distinct_batches=1)
+    return {"value": r["samples_per_sec"], "unit": "samples/s", "cores": world * threads, "host_cores": cores, "kind": "reference",
+            "sample": f"{args.model} fp32, stock torch DDP over gloo (what RayAccelerator(use_gpu=False) runs, ray_ddp.py:227), "
+                      f"{world} workers x {threads} threads, batch {args.ref_batch}/worker, 2 timed steps after 1 warm-up"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b2c", choices=["b2c", "reference"])
+    ap.add_argument("--model", default="resnet50")
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--wire", default="f32", choices=["f32", "bf16"])
+    ap.add_argument("--ar-iters", type=int, default=15)
+    ap.add_argument("--ref-batch", type=int, default=16)
+    ap.add_argument("--ref-max-steps", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b2c(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -12,6 +12,7 @@ ray.tune is absent from this image, so `tune` resolves to a minimal in-process s
 installed the import below picks it up instead.
 """
 import contextlib
+import functools
 import os
 from typing import Dict, List, Union
 
@@ -62,6 +63,17 @@ except ImportError:
 
     def is_session_enabled():
         return tune.is_session_enabled()
+
+
+def _tune_report(report):
+    """Module-level on purpose: the queued item is pickled BY REFERENCE to this function, so it
+    runs against the driver's `tune` (the live trial session), not a copy of the worker's."""
+    tune.report(**report)
+
+
+def _tune_checkpoint(checkpoint_dict, global_step, filename):
+    with tune.checkpoint_dir(step=global_step) as checkpoint_dir:
+        atomic_save(checkpoint_dict, os.path.join(checkpoint_dir, filename))
 
 
 def atomic_save(checkpoint, filepath):
@@ -121,7 +133,7 @@ class TuneReportCallback(TuneCallback):
         if get_actor_rank() == 0:
             report = self._get_report_dict(trainer, pl_module)
             if report is not None:
-                put_queue(lambda: tune.report(**report))
+                put_queue(functools.partial(_tune_report, report))
 
 
 class _TuneCheckpointCallback(TuneCallback):
@@ -133,8 +145,7 @@ class _TuneCheckpointCallback(TuneCallback):
 
     @staticmethod
     def _create_checkpoint(checkpoint_dict: dict, global_step: int, filename: str):
-        with tune.checkpoint_dir(step=global_step) as checkpoint_dir:
-            atomic_save(checkpoint_dict, os.path.join(checkpoint_dir, filename))
+        _tune_checkpoint(checkpoint_dict, global_step, filename)
 
     def _handle(self, trainer, pl_module):
         if getattr(trainer, "running_sanity_check", False):
@@ -142,8 +153,7 @@ class _TuneCheckpointCallback(TuneCallback):
         checkpoint_dict = trainer.checkpoint_connector.dump_checkpoint()
         global_step = trainer.global_step
         if get_actor_rank() == 0:
-            filename = self._filename
-            put_queue(lambda: _TuneCheckpointCallback._create_checkpoint(checkpoint_dict, global_step, filename))
+            put_queue(functools.partial(_tune_checkpoint, checkpoint_dict, global_step, self._filename))
 
 
 class TuneReportCheckpointCallback(TuneCallback):

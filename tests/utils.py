@@ -72,9 +72,9 @@ def get_trainer(dir, accelerator, use_gpu=False, max_epochs=1, limit_train_batch
 def train_test(trainer, model):
     """fit() == 1 and the DRIVER's copy of the weights moved by > 0.1: rank 0's weights really
     came back (ray_ddp.py:185-189)."""
-    initial = torch.tensor([torch.sum(torch.abs(x)) for x in model.parameters()])
+    initial = torch.tensor([float(torch.sum(torch.abs(x.detach()))) for x in model.parameters()])
     result = trainer.fit(model)
-    post = torch.tensor([torch.sum(torch.abs(x)) for x in model.parameters()])
+    post = torch.tensor([float(torch.sum(torch.abs(x.detach()))) for x in model.parameters()])
     assert result == 1, "trainer failed"
     assert torch.norm(initial - post) > 0.1
 
