@@ -49,6 +49,8 @@ enum {
   B2C_ALGO_AUTO = 0,          /* one-shot below the crossover, two-shot above */
   B2C_ALGO_ONESHOT = 1,       /* every rank pulls all W copies and reduces locally */
   B2C_ALGO_TWOSHOT = 2,       /* reduce-scatter then all-gather (variant by param) */
+  B2C_ALGO_NVLS = 3,          /* in-switch reduction: multimem.ld_reduce + multimem.st on the
+                                 multicast arena (needs b2c_nvls_* set-up) */
 };
 
 /* keys for b2c_set_param / b2c_get_param */
@@ -64,7 +66,10 @@ enum {
                                      buffers with no staging; 0: always stage through the arena */
   B2C_PARAM_ZEROCOPY_MIN_BYTES = 8, /* AUTO: at or above this size a registered buffer uses the
                                      zero-copy two-shot even below the one-shot crossover */
-  B2C_PARAM__COUNT = 9
+  B2C_PARAM_NVLS_MIN_BYTES = 9,   /* AUTO: wire bytes at or above which the NVLS path is used when
+                                     the multicast arena is up (0 = never pick it automatically) */
+  B2C_PARAM_MAX_BLOCKS_NVLS = 10,
+  B2C_PARAM__COUNT = 11
 };
 
 /* error codes */
@@ -88,6 +93,7 @@ typedef struct b2c_stats {
   uint64_t oneshot_launches;
   uint64_t twoshot_launches;
   uint64_t zerocopy_launches;
+  uint64_t nvls_launches;
   uint32_t last_algo;           /* B2C_ALGO_* actually used by the last allreduce */
   uint32_t last_blocks;         /* grid.x of the last launch */
   uint32_t last_threads;
@@ -167,6 +173,29 @@ int b2c_group_barrier(b2c_comm** comms, b2c_stream_t stream);
 int b2c_register_export(b2c_comm* comm, void* ptr, size_t bytes, void* blob, size_t* len);
 int b2c_register_import(b2c_comm* comm, void* ptr, size_t bytes, const void* blobs, size_t len_each);
 int b2c_deregister(b2c_comm* comm, void* ptr);
+
+/* ---- NVLS (NVLink SHARP) multicast arena ---------------------------------
+ * A second symmetric arena, allocated with cuMemCreate and bound to an NVLink multicast
+ * object, so that the switch does the reduction (multimem.ld_reduce) and the replication
+ * (multimem.st): each GPU moves ~S bytes per direction instead of 2(W-1)/W*S, which is the
+ * only way past the peer-to-peer ceiling for the large DDP buckets.  Optional: without it
+ * every other path keeps working.  Collective, three phases with a host barrier between
+ * import and bind (every device must have been added before any memory is bound):
+ *   b2c_nvls_export  allocate local memory; rank 0 creates the multicast object; fill blob
+ *   b2c_nvls_import  blobs in rank order: adopt rank 0's multicast handle, add this device
+ *   -- host barrier --
+ *   b2c_nvls_bind    bind + map (unicast and multicast views); -- host barrier -- ready
+ * b2c_nvls_arena returns the local unicast view: tensors placed inside it are reduced in
+ * place (no staging) when passed to b2c_allreduce with algo NVLS/AUTO at the same offset on
+ * every rank.  Arithmetic: the switch adds in fp32 in its own order and the result is scaled
+ * afterwards (sum * scale): within the stated tolerances of the reference path, bitwise
+ * identical across replicas, but NOT bit-identical to the rank-order contract of the other
+ * algorithms.  No reference counterpart (NCCL's NVLS algorithm is the upstream analogue). */
+#define B2C_NVLS_BLOB_BYTES 64
+int b2c_nvls_export(b2c_comm* comm, size_t bytes, void* blob, size_t* len);
+int b2c_nvls_import(b2c_comm* comm, const void* blobs, size_t len_each);
+int b2c_nvls_bind(b2c_comm* comm);
+int b2c_nvls_arena(b2c_comm* comm, void** base, size_t* bytes);
 
 /* ---- knobs, counters, introspection ------------------------------------ */
 int b2c_set_param(b2c_comm* comm, int key, long value);

@@ -16,7 +16,7 @@ HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b2c.h")
 
 # mirrors of the enums in include/b2c.h
 F32, BF16, U8 = 0, 1, 2
-ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT = 0, 1, 2
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2, 3
 PARAM_CROSSOVER_BYTES = 0
 PARAM_MAX_BLOCKS_ONESHOT = 1
 PARAM_MAX_BLOCKS_TWOSHOT = 2
@@ -26,7 +26,10 @@ PARAM_TWOSHOT_VARIANT = 5
 PARAM_MAX_BLOCKS_BCAST = 6
 PARAM_ZEROCOPY = 7
 PARAM_ZEROCOPY_MIN_BYTES = 8
+PARAM_NVLS_MIN_BYTES = 9
+PARAM_MAX_BLOCKS_NVLS = 10
 REG_BLOB_BYTES = 128
+NVLS_BLOB_BYTES = 64
 MAX_WORLD = 8
 MAX_BLOCKS = 256
 EXPORT_BLOB_BYTES = 256
@@ -56,6 +59,7 @@ class Stats(ctypes.Structure):
         ("oneshot_launches", ctypes.c_uint64),
         ("twoshot_launches", ctypes.c_uint64),
         ("zerocopy_launches", ctypes.c_uint64),
+        ("nvls_launches", ctypes.c_uint64),
         ("last_algo", ctypes.c_uint32),
         ("last_blocks", ctypes.c_uint32),
         ("last_threads", ctypes.c_uint32),
@@ -93,6 +97,10 @@ SIGNATURES = {
     "b2c_register_export": (_int, [_vp, _vp, _sz, _vp, _c.POINTER(_sz)]),
     "b2c_register_import": (_int, [_vp, _vp, _sz, _vp, _sz]),
     "b2c_deregister": (_int, [_vp, _vp]),
+    "b2c_nvls_export": (_int, [_vp, _sz, _vp, _c.POINTER(_sz)]),
+    "b2c_nvls_import": (_int, [_vp, _vp, _sz]),
+    "b2c_nvls_bind": (_int, [_vp]),
+    "b2c_nvls_arena": (_int, [_vp, _pp, _c.POINTER(_sz)]),
     "b2c_set_param": (_int, [_vp, _int, _c.c_long]),
     "b2c_get_param": (_int, [_vp, _int, _c.POINTER(_c.c_long)]),
     "b2c_get_stats": (_int, [_vp, _c.POINTER(Stats)]),

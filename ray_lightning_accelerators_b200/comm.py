@@ -11,7 +11,7 @@ import os
 import torch
 
 from . import _lib
-from ._lib import (ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, BF16, F32, U8, B2cError)  # noqa: F401
+from ._lib import (ALGO_AUTO, ALGO_NVLS, ALGO_ONESHOT, ALGO_TWOSHOT, BF16, F32, U8, B2cError)  # noqa: F401
 
 _DTYPES = {torch.float32: F32, torch.bfloat16: BF16}
 _ELEM = {F32: 4, BF16: 2}
@@ -29,6 +29,8 @@ _ENV_PARAMS = {
     "B2C_TWOSHOT_VARIANT": _lib.PARAM_TWOSHOT_VARIANT,
     "B2C_ZEROCOPY": _lib.PARAM_ZEROCOPY,
     "B2C_ZEROCOPY_MIN_BYTES": _lib.PARAM_ZEROCOPY_MIN_BYTES,
+    "B2C_NVLS_MIN_BYTES": _lib.PARAM_NVLS_MIN_BYTES,
+    "B2C_MAX_BLOCKS_NVLS": _lib.PARAM_MAX_BLOCKS_NVLS,
 }
 
 
@@ -102,6 +104,8 @@ class Comm(_Base):
         self._first = h
         self._exchange = exchange
         self._registered = {}
+        self._nvls = False
+        self.nvls_error = None
         self._apply_env()
         if self.world > 1:
             if exchange is None:
@@ -159,6 +163,58 @@ class Comm(_Base):
                                                      _lib.REG_BLOB_BYTES))
         self._registered[key] = ok
         return ok
+
+    def enable_nvls(self, arena_bytes=512 << 20):
+        """Collective: set up the NVLink-multicast arena (in-switch reduction).  Returns True when
+        every rank succeeded; on False nothing changes and the peer-to-peer paths keep working."""
+        if self.world < 2 or self._nvls:
+            return self._nvls
+        blob = ctypes.create_string_buffer(_lib.NVLS_BLOB_BYTES)
+        n = ctypes.c_size_t(_lib.NVLS_BLOB_BYTES)
+        rc = self._lib.b2c_nvls_export(self._h, int(arena_bytes), blob, ctypes.byref(n))
+        self.nvls_error = None if rc == 0 else _lib.last_error()
+        blobs = self._exchange(blob.raw if rc == 0 else None)
+        if any(b is None for b in blobs):
+            return False
+        joined = b"".join(bytes(b) for b in blobs)
+        rc = self._lib.b2c_nvls_import(self._h, joined, _lib.NVLS_BLOB_BYTES)
+        if rc != 0:
+            self.nvls_error = _lib.last_error()
+        oks = self._exchange(rc == 0)      # doubles as the barrier: every device added before any bind
+        if not all(oks):
+            return False
+        rc = self._lib.b2c_nvls_bind(self._h)
+        if rc != 0:
+            self.nvls_error = _lib.last_error()
+        oks = self._exchange(rc == 0)      # every rank bound before the first multimem access
+        self._nvls = all(oks)
+        if self._nvls:
+            base, nbytes = ctypes.c_void_p(), ctypes.c_size_t()
+            _lib.check(self._lib.b2c_nvls_arena(self._h, ctypes.byref(base), ctypes.byref(nbytes)))
+            self._nvls_base, self._nvls_bytes, self._nvls_top = base.value, nbytes.value, 0
+        return self._nvls
+
+    def nvls_empty(self, numel, dtype=torch.float32):
+        """A tensor INSIDE the multicast arena (bump allocation, 256-byte aligned, never freed):
+        allreduce on it runs in place in the switch with no staging.  Every rank must allocate
+        the same sequence of sizes so that offsets match."""
+        if not self._nvls:
+            raise RuntimeError("multicast arena is not set up (enable_nvls)")
+        es = torch.empty(0, dtype=dtype).element_size()
+        nbytes = (numel * es + 255) // 256 * 256
+        if self._nvls_top + nbytes > self._nvls_bytes:
+            raise MemoryError(f"multicast arena exhausted ({self._nvls_bytes} bytes)")
+        ptr = self._nvls_base + self._nvls_top
+        self._nvls_top += nbytes
+
+        class _Raw:  # __cuda_array_interface__ v3: zero-copy view of raw device memory
+            pass
+
+        raw = _Raw()
+        raw.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3,
+                                        "strides": None}
+        flat = torch.as_tensor(raw, device=torch.device("cuda", self.device))
+        return flat[:numel * es].view(dtype)
 
     def deregister(self, t):
         key = (t.data_ptr(), t.numel() * t.element_size())

@@ -5,6 +5,9 @@
 #include <string.h>
 #include <stdlib.h>
 #include <unistd.h>
+#include <sys/syscall.h>
+#include <errno.h>
+#include <cuda.h>   // types only: the driver API is reached through cudaGetDriverEntryPoint (no -lcuda)
 
 #include "b2c_kernels.cuh"
 
@@ -78,8 +81,17 @@ struct b2c_comm {
   int nregs, regs_cap;
   struct OpenedHandle* opened;       // IPC base allocations already mapped (one open per handle)
   int nopened, opened_cap;
+  struct Nvls* nvls;                 // multicast arena (optional)
 };
 
+struct Nvls {
+  int phase;                              // 1 exported, 2 imported, 3 bound (usable)
+  size_t bytes, slot_bytes;
+  CUmemGenericAllocationHandle mem, mc;
+  int mc_fd;                              // rank 0: exported fd of the multicast object
+  CUdeviceptr uc, mcva;
+  bool uc_mapped, mc_mapped, bound;
+};
 struct Registration {
   char* local;                       // caller pointer on this rank
   size_t bytes;
@@ -103,6 +115,8 @@ struct RegBlob {
 };
 static_assert(sizeof(RegBlob) <= B2C_REG_BLOB_BYTES, "reg blob too large");
 
+static void nvls_release(b2c_comm* c);
+
 static uint64_t host_identity() {
   uint64_t h = (uint64_t)gethostid();
   FILE* f = fopen("/proc/sys/kernel/random/boot_id", "r");
@@ -125,6 +139,8 @@ static void default_params(b2c_comm* c) {
   c->params[B2C_PARAM_MAX_BLOCKS_BCAST] = 32;
   c->params[B2C_PARAM_ZEROCOPY] = 1;
   c->params[B2C_PARAM_ZEROCOPY_MIN_BYTES] = 256 * 1024;
+  c->params[B2C_PARAM_NVLS_MIN_BYTES] = 2 * 1024 * 1024;
+  c->params[B2C_PARAM_MAX_BLOCKS_NVLS] = 64;
 }
 
 static int comm_alloc(int rank, int world, int device, size_t arena_bytes, b2c_comm** out) {
@@ -249,6 +265,7 @@ extern "C" int b2c_comm_destroy(b2c_comm* c) {
       cudaError_t e = cudaIpcCloseMemHandle(c->peer_region[q]);
       if (e != cudaSuccess && rc == B2C_OK) rc = cuda_fail(e, "cudaIpcCloseMemHandle");
     }
+  nvls_release(c);
   for (int i = 0; i < c->nopened; ++i)
     if (c->opened[i].base) cudaIpcCloseMemHandle(c->opened[i].base);
   free(c->opened);
@@ -360,6 +377,18 @@ static void geometry(const b2c_comm* c, size_t nvec_span, long max_blocks, int* 
   *nblocks = (int)nb; *threads = (int)th; *chunk_vecs = (uint32_t)cv;
 }
 
+// W == 1 only: not limited by the flag-channel count
+static void geometry_wide(const b2c_comm* c, size_t nvec, long max_blocks, int* nblocks, int* threads, uint32_t* chunk_vecs) {
+  const size_t th = (size_t)c->params[B2C_PARAM_THREADS];
+  size_t cu = (nvec + th * max_blocks - 1) / (th * max_blocks);
+  if (cu < 1) cu = 1;
+  if (cu > 8) cu = 8;
+  size_t nb = (nvec + th * cu - 1) / (th * cu);
+  if (nb < 1) nb = 1;
+  if (nb > (size_t)max_blocks) nb = max_blocks;
+  *nblocks = (int)nb; *threads = (int)th; *chunk_vecs = (uint32_t)(th * cu);
+}
+
 // local group: all W virtual ranks' CTAs must be co-resident (cooperative launch), so the
 // per-rank channel count is capped at (resident CTAs on the device) / W
 static long group_block_cap(const b2c_comm* c, const void* fn, long want) {
@@ -443,7 +472,7 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
   int mode, vw, ub;
   rc = mode_of(dtype, wire, &mode, &vw, &ub);
   if (rc) return rc;
-  if (algo < B2C_ALGO_AUTO || algo > B2C_ALGO_TWOSHOT) return fail(B2C_EINVAL, "b2c_allreduce: algo=%d", algo);
+  if (algo < B2C_ALGO_AUTO || algo > B2C_ALGO_NVLS) return fail(B2C_EINVAL, "b2c_allreduce: algo=%d", algo);
   c->stats.calls_allreduce++;
   c->stats.bytes_allreduce += (uint64_t)count * ub;
   if (count == 0) return B2C_OK;
@@ -454,6 +483,40 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
     if ((uintptr_t)bufs[r] % ub) return fail(B2C_EINVAL, "b2c_allreduce: buf %p is not aligned to its element size %d", bufs[r], ub);
   }
   DeviceGuard g(c->device);
+
+  // ---- NVLS: in-switch reduction on the multicast arena
+  const bool nvls_up = !group && c->nvls && c->nvls->phase == 3;
+  if (algo == B2C_ALGO_NVLS && !nvls_up)
+    return fail(B2C_ESTATE, "b2c_allreduce: algo NVLS requested but the multicast arena is not set up (b2c_nvls_export/import/bind)");
+  if (nvls_up && W > 1 && mode != MODE_F32_BF16 &&
+      (algo == B2C_ALGO_NVLS || (algo == B2C_ALGO_AUTO && c->params[B2C_PARAM_NVLS_MIN_BYTES] > 0 &&
+                                 count * (size_t)ub >= (size_t)c->params[B2C_PARAM_NVLS_MIN_BYTES]))) {
+    Nvls* nv = c->nvls;
+    char* p = (char*)bufs[c->rank];
+    const bool inside = p >= (char*)nv->uc && p + count * ub <= (char*)nv->uc + nv->bytes && (((uintptr_t)p & 15u) == 0);
+    const size_t piece = inside ? count : (nv->slot_bytes / 16) * vw;
+    for (size_t off = 0; off < count; off += piece) {
+      const size_t n = (count - off < piece) ? count - off : piece;
+      Launch L;
+      fill_common(c, L.args, false);
+      L.args.buf[c->rank] = p + off * ub;
+      L.args.count = n;
+      L.args.scale = scale;
+      L.args.nvls_uc = (char*)nv->uc;
+      L.args.nvls_mc = (char*)nv->mcva;
+      L.args.nvls_slot_bytes = nv->slot_bytes;
+      L.args.nvls_inplace = inside ? 1 : 0;
+      L.args.nvls_off = inside ? (size_t)(p - (char*)nv->uc) : 0;
+      const size_t nvec = (n + vw - 1) / vw;
+      L.fn = mode == MODE_F32 ? (const void*)k_allreduce_nvls<MODE_F32> : (const void*)k_allreduce_nvls<MODE_BF16>;
+      geometry(c, (nvec + W - 1) / W, c->params[B2C_PARAM_MAX_BLOCKS_NVLS], &L.nblocks, &L.threads, &L.args.chunk_vecs);
+      c->stats.nvls_launches++;
+      c->stats.last_algo = B2C_ALGO_NVLS;
+      rc = do_launch(c, L, 1, stream);
+      if (rc) return rc;
+    }
+    return B2C_OK;
+  }
 
   // ---- zero-copy two-shot: the buffers themselves are peer-visible (local group, or registered)
   if (W > 1 && c->params[B2C_PARAM_ZEROCOPY] && mode != MODE_F32_BF16 && algo != B2C_ALGO_ONESHOT &&
@@ -503,6 +566,10 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
       L.fn = mode == MODE_F32 ? oneshot_fn<MODE_F32>(W) : mode == MODE_BF16 ? oneshot_fn<MODE_BF16>(W) : oneshot_fn<MODE_F32_BF16>(W);
       long mb = c->params[B2C_PARAM_MAX_BLOCKS_ONESHOT];
       if (group) mb = group_block_cap(c, L.fn, mb);
+      if (W == 1) {
+        // no peer, no flags: a plain HBM-bound scale pass, so fill the whole chip (several CTAs per SM)
+        geometry_wide(c, nvec, 148 * 4, &L.nblocks, &L.threads, &L.args.chunk_vecs);
+      } else
       geometry(c, nvec, mb, &L.nblocks, &L.threads, &L.args.chunk_vecs);
       c->stats.oneshot_launches++;
     } else {
@@ -606,6 +673,217 @@ extern "C" int b2c_group_barrier(b2c_comm** comms, b2c_stream_t stream) {
   int rc = group_check(comms, "b2c_group_barrier");
   if (rc) return rc;
   return barrier_impl(comms[0], true, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------- NVLS multicast arena
+struct NvlsBlob {
+  uint32_t magic;
+  int32_t rank;
+  int64_t pid;
+  int32_t mc_fd;
+  int32_t pad0;
+  uint64_t bytes;
+};
+static_assert(sizeof(NvlsBlob) <= B2C_NVLS_BLOB_BYTES, "nvls blob too large");
+
+struct Drv {
+  decltype(&cuDeviceGet) DeviceGet;
+  decltype(&cuMemCreate) MemCreate;
+  decltype(&cuMemRelease) MemRelease;
+  decltype(&cuMemGetAllocationGranularity) MemGetAllocationGranularity;
+  decltype(&cuMemAddressReserve) MemAddressReserve;
+  decltype(&cuMemAddressFree) MemAddressFree;
+  decltype(&cuMemMap) MemMap;
+  decltype(&cuMemUnmap) MemUnmap;
+  decltype(&cuMemSetAccess) MemSetAccess;
+  decltype(&cuMemExportToShareableHandle) MemExportToShareableHandle;
+  decltype(&cuMemImportFromShareableHandle) MemImportFromShareableHandle;
+  decltype(&cuMulticastCreate) MulticastCreate;
+  decltype(&cuMulticastAddDevice) MulticastAddDevice;
+  decltype(&cuMulticastBindMem) MulticastBindMem;
+  decltype(&cuMulticastGetGranularity) MulticastGetGranularity;
+  decltype(&cuGetErrorString) GetErrorString;
+  bool ok;
+};
+static Drv* drv() {
+  static Drv d;
+  static bool tried = false;
+  if (tried) return d.ok ? &d : nullptr;
+  tried = true;
+  cudaDriverEntryPointQueryResult qr;
+  bool ok = true;
+#define B2C_SYM(field, name) ok = ok && (cudaGetDriverEntryPoint(name, (void**)&d.field, cudaEnableDefault, &qr) == cudaSuccess) && d.field
+  B2C_SYM(DeviceGet, "cuDeviceGet");
+  B2C_SYM(MemCreate, "cuMemCreate");
+  B2C_SYM(MemRelease, "cuMemRelease");
+  B2C_SYM(MemGetAllocationGranularity, "cuMemGetAllocationGranularity");
+  B2C_SYM(MemAddressReserve, "cuMemAddressReserve");
+  B2C_SYM(MemAddressFree, "cuMemAddressFree");
+  B2C_SYM(MemMap, "cuMemMap");
+  B2C_SYM(MemUnmap, "cuMemUnmap");
+  B2C_SYM(MemSetAccess, "cuMemSetAccess");
+  B2C_SYM(MemExportToShareableHandle, "cuMemExportToShareableHandle");
+  B2C_SYM(MemImportFromShareableHandle, "cuMemImportFromShareableHandle");
+  B2C_SYM(MulticastCreate, "cuMulticastCreate");
+  B2C_SYM(MulticastAddDevice, "cuMulticastAddDevice");
+  B2C_SYM(MulticastBindMem, "cuMulticastBindMem");
+  B2C_SYM(MulticastGetGranularity, "cuMulticastGetGranularity");
+  B2C_SYM(GetErrorString, "cuGetErrorString");
+#undef B2C_SYM
+  cudaGetLastError();
+  d.ok = ok;
+  return ok ? &d : nullptr;
+}
+static int drv_fail(Drv* d, CUresult r, const char* what) {
+  const char* msg = nullptr;
+  if (d) d->GetErrorString(r, &msg);
+  return fail(B2C_EUNSUPPORTED, "b2c_nvls: %s failed: driver error %d (%s)", what, (int)r, msg ? msg : "?");
+}
+#define DRV(call, what)                                  \
+  do {                                                   \
+    CUresult r_ = (call);                                \
+    if (r_ != CUDA_SUCCESS) return drv_fail(d, r_, what); \
+  } while (0)
+
+static void nvls_release(b2c_comm* c) {
+  Nvls* n = c->nvls;
+  Drv* d = drv();
+  if (!n) return;
+  if (d) {
+    if (n->mc_mapped) { d->MemUnmap(n->mcva, n->bytes); d->MemAddressFree(n->mcva, n->bytes); }
+    if (n->uc_mapped) { d->MemUnmap(n->uc, n->bytes); d->MemAddressFree(n->uc, n->bytes); }
+    if (n->mc) d->MemRelease(n->mc);
+    if (n->mem) d->MemRelease(n->mem);
+  }
+  if (n->mc_fd > 0) close(n->mc_fd);
+  free(n);
+  c->nvls = nullptr;
+}
+
+extern "C" int b2c_nvls_export(b2c_comm* c, size_t bytes, void* blob, size_t* len) {
+  if (!c || !blob || !len) return fail(B2C_EINVAL, "b2c_nvls_export: NULL argument");
+  if (*len < B2C_NVLS_BLOB_BYTES) return fail(B2C_EINVAL, "b2c_nvls_export: blob needs %d bytes", B2C_NVLS_BLOB_BYTES);
+  if (c->local_group || c->world < 2) return fail(B2C_ESTATE, "b2c_nvls_export: needs a cross-process comm with world >= 2");
+  if (!c->ready) return fail(B2C_ESTATE, "b2c_nvls_export: comm not imported yet");
+  if (c->nvls) return fail(B2C_ESTATE, "b2c_nvls_export: already set up");
+  DeviceGuard g(c->device);
+  cudaFree(0);
+  Drv* d = drv();
+  if (!d) return fail(B2C_EUNSUPPORTED, "b2c_nvls_export: this driver has no multicast entry points");
+  CUdevice dev;
+  DRV(d->DeviceGet(&dev, c->device), "cuDeviceGet");
+  CUmulticastObjectProp mp;
+  memset(&mp, 0, sizeof(mp));
+  mp.numDevices = (unsigned)c->world;
+  mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  mp.size = bytes;
+  size_t mgran = 0, agran = 0;
+  DRV(d->MulticastGetGranularity(&mgran, &mp, CU_MULTICAST_GRANULARITY_MINIMUM), "cuMulticastGetGranularity");
+  CUmemAllocationProp ap;
+  memset(&ap, 0, sizeof(ap));
+  ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  ap.location.id = c->device;
+  ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  DRV(d->MemGetAllocationGranularity(&agran, &ap, CU_MEM_ALLOC_GRANULARITY_MINIMUM), "cuMemGetAllocationGranularity");
+  size_t gran = mgran > agran ? mgran : agran;
+  size_t size = (bytes + gran - 1) / gran * gran;
+  Nvls* n = (Nvls*)calloc(1, sizeof(Nvls));
+  n->bytes = size;
+  n->slot_bytes = (size / 2) & ~(size_t)255;
+  n->mc_fd = -1;
+  c->nvls = n;
+  CUresult r = d->MemCreate(&n->mem, size, &ap, 0);
+  if (r != CUDA_SUCCESS) { nvls_release(c); return drv_fail(d, r, "cuMemCreate"); }
+  if (c->rank == 0) {
+    mp.size = size;
+    r = d->MulticastCreate(&n->mc, &mp);
+    if (r != CUDA_SUCCESS) { nvls_release(c); return drv_fail(d, r, "cuMulticastCreate"); }
+    r = d->MemExportToShareableHandle(&n->mc_fd, n->mc, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+    if (r != CUDA_SUCCESS) { nvls_release(c); return drv_fail(d, r, "cuMemExportToShareableHandle(multicast)"); }
+  }
+  NvlsBlob b;
+  memset(&b, 0, sizeof(b));
+  b.magic = B2C_MAGIC ^ 0x33333333u;
+  b.rank = c->rank; b.pid = (int64_t)getpid(); b.mc_fd = n->mc_fd; b.bytes = size;
+  memset(blob, 0, B2C_NVLS_BLOB_BYTES);
+  memcpy(blob, &b, sizeof(b));
+  *len = B2C_NVLS_BLOB_BYTES;
+  n->phase = 1;
+  return B2C_OK;
+}
+
+extern "C" int b2c_nvls_import(b2c_comm* c, const void* blobs, size_t len_each) {
+  if (!c || !blobs) return fail(B2C_EINVAL, "b2c_nvls_import: NULL argument");
+  if (!c->nvls || c->nvls->phase != 1) return fail(B2C_ESTATE, "b2c_nvls_import: call b2c_nvls_export first");
+  if (len_each < sizeof(NvlsBlob)) return fail(B2C_EINVAL, "b2c_nvls_import: len_each too small");
+  DeviceGuard g(c->device);
+  Drv* d = drv();
+  Nvls* n = c->nvls;
+  NvlsBlob b0;
+  memcpy(&b0, blobs, sizeof(b0));
+  for (int q = 0; q < c->world; ++q) {
+    NvlsBlob b;
+    memcpy(&b, (const char*)blobs + (size_t)q * len_each, sizeof(b));
+    if (b.magic != (B2C_MAGIC ^ 0x33333333u) || b.rank != q) return fail(B2C_EINVAL, "b2c_nvls_import: blob %d malformed / out of order", q);
+    if (b.bytes != n->bytes) return fail(B2C_EINVAL, "b2c_nvls_import: rank %d arena %llu B != ours %zu B", q, (unsigned long long)b.bytes, n->bytes);
+  }
+  if (c->rank != 0) {
+    // fetch rank 0's file descriptor: pidfd_open + pidfd_getfd (Linux >= 5.6, same user / CAP_SYS_PTRACE)
+#if defined(SYS_pidfd_open) && defined(SYS_pidfd_getfd)
+    int pidfd = (int)syscall(SYS_pidfd_open, (pid_t)b0.pid, 0);
+    if (pidfd < 0) return fail(B2C_EUNSUPPORTED, "b2c_nvls_import: pidfd_open(%lld) failed (errno %d)", (long long)b0.pid, errno);
+    int fd = (int)syscall(SYS_pidfd_getfd, pidfd, b0.mc_fd, 0);
+    int err = errno;
+    close(pidfd);
+    if (fd < 0) return fail(B2C_EUNSUPPORTED, "b2c_nvls_import: pidfd_getfd failed (errno %d); ranks must share a user / ptrace scope", err);
+    CUresult r = d->MemImportFromShareableHandle(&n->mc, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+    close(fd);
+    if (r != CUDA_SUCCESS) return drv_fail(d, r, "cuMemImportFromShareableHandle(multicast)");
+#else
+    return fail(B2C_EUNSUPPORTED, "b2c_nvls_import: built without pidfd syscalls");
+#endif
+  }
+  CUdevice dev;
+  DRV(d->DeviceGet(&dev, c->device), "cuDeviceGet");
+  DRV(d->MulticastAddDevice(n->mc, dev), "cuMulticastAddDevice");
+  n->phase = 2;
+  return B2C_OK;
+}
+
+extern "C" int b2c_nvls_bind(b2c_comm* c) {
+  if (!c) return fail(B2C_EINVAL, "b2c_nvls_bind: comm is NULL");
+  if (!c->nvls || c->nvls->phase != 2) return fail(B2C_ESTATE, "b2c_nvls_bind: call b2c_nvls_import (on every rank, then a barrier) first");
+  DeviceGuard g(c->device);
+  Drv* d = drv();
+  Nvls* n = c->nvls;
+  DRV(d->MulticastBindMem(n->mc, 0, n->mem, 0, n->bytes, 0), "cuMulticastBindMem");
+  n->bound = true;
+  CUmemAccessDesc acc;
+  memset(&acc, 0, sizeof(acc));
+  acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  acc.location.id = c->device;
+  acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  DRV(d->MemAddressReserve(&n->uc, n->bytes, 0, 0, 0), "cuMemAddressReserve(uc)");
+  DRV(d->MemMap(n->uc, n->bytes, 0, n->mem, 0), "cuMemMap(uc)");
+  n->uc_mapped = true;
+  DRV(d->MemSetAccess(n->uc, n->bytes, &acc, 1), "cuMemSetAccess(uc)");
+  DRV(d->MemAddressReserve(&n->mcva, n->bytes, 0, 0, 0), "cuMemAddressReserve(mc)");
+  DRV(d->MemMap(n->mcva, n->bytes, 0, n->mc, 0), "cuMemMap(mc)");
+  n->mc_mapped = true;
+  DRV(d->MemSetAccess(n->mcva, n->bytes, &acc, 1), "cuMemSetAccess(mc)");
+  CU(cudaMemset((void*)n->uc, 0, n->bytes));
+  CU(cudaDeviceSynchronize());
+  n->phase = 3;
+  return B2C_OK;
+}
+
+extern "C" int b2c_nvls_arena(b2c_comm* c, void** base, size_t* bytes) {
+  if (!c) return fail(B2C_EINVAL, "b2c_nvls_arena: comm is NULL");
+  if (!c->nvls || c->nvls->phase != 3) return fail(B2C_ESTATE, "b2c_nvls_arena: multicast arena is not set up");
+  if (base) *base = (void*)c->nvls->uc;
+  if (bytes) *bytes = c->nvls->bytes;
+  return B2C_OK;
 }
 
 // ---------------------------------------------------------------- registered buffers
@@ -730,6 +1008,7 @@ extern "C" int b2c_set_param(b2c_comm* c, int key, long v) {
     case B2C_PARAM_MAX_BLOCKS_ONESHOT:
     case B2C_PARAM_MAX_BLOCKS_TWOSHOT:
     case B2C_PARAM_MAX_BLOCKS_BCAST:
+    case B2C_PARAM_MAX_BLOCKS_NVLS:
       if (v < 1 || v > B2C_MAX_BLOCKS) return fail(B2C_EINVAL, "b2c_set_param: blocks=%ld must be 1..%d", v, B2C_MAX_BLOCKS);
       break;
     case B2C_PARAM_TIMEOUT_MS:
@@ -742,6 +1021,7 @@ extern "C" int b2c_set_param(b2c_comm* c, int key, long v) {
       if (v != 0 && v != 1) return fail(B2C_EINVAL, "b2c_set_param: zerocopy=%ld (0 or 1)", v);
       break;
     case B2C_PARAM_ZEROCOPY_MIN_BYTES:
+    case B2C_PARAM_NVLS_MIN_BYTES:
     case B2C_PARAM_CROSSOVER_BYTES:
       if (v < 0) return fail(B2C_EINVAL, "b2c_set_param: crossover=%ld", v);
       break;

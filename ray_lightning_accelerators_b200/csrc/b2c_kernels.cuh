@@ -47,6 +47,12 @@ struct B2cKArgs {
   int root;
   int variant;
   uint32_t chunk_vecs;             // ownership granularity (16-byte vectors), multiple of blockDim.x
+  // NVLS path only
+  char* nvls_uc;                   // local unicast view of the multicast arena
+  char* nvls_mc;                   // multicast view (multimem.* only)
+  size_t nvls_slot_bytes;          // staged mode: arena is two slots, picked by call parity
+  size_t nvls_off;                 // in-place mode: offset of the caller's tensor inside the arena
+  int nvls_inplace;
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -567,5 +573,104 @@ __global__ void __launch_bounds__(512, 1) k_allreduce_twoshot_zc(const __grid_co
     }
   }
   channel_barrier(a, c, c.epoch + 2u);
+  epilogue(c);
+}
+
+
+// ================================================================= NVLS allreduce (in-switch reduction)
+// multimem.ld_reduce on a multicast address returns the SUM over every GPU's copy (the NVSwitch
+// adds, fp32 accumulate); multimem.st writes one value into every GPU's copy.  Each rank reduces
+// its own shard and broadcasts it, so a GPU moves ~S bytes per direction instead of 2(W-1)/W*S.
+//   staged  : stage bucket -> local arena slot; barrier A; ld_reduce / scale / multimem.st (+ own
+//             bucket directly); barrier B; copy the other shards from the local arena into the bucket
+//   in place: the tensor lives in the arena: barrier A; ld_reduce / scale / multimem.st; barrier B
+// World size is a runtime value here (the switch does the W-way add).
+__device__ __forceinline__ uint4 multimem_ld_reduce_f32(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_v4(void* mc, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <int MODE>
+__device__ __forceinline__ uint4 nvls_scale(uint4 v, float scale) {
+  if (MODE == MODE_F32) {
+    return make_uint4(__float_as_uint(__fmul_rn(__uint_as_float(v.x), scale)), __float_as_uint(__fmul_rn(__uint_as_float(v.y), scale)),
+                      __float_as_uint(__fmul_rn(__uint_as_float(v.z), scale)), __float_as_uint(__fmul_rn(__uint_as_float(v.w), scale)));
+  } else {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o[k] = pack_bf16x2(__fmul_rn(bf16_lo(w[k]), scale), __fmul_rn(bf16_hi(w[k]), scale));
+    return make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(512, 1) k_allreduce_nvls(const __grid_constant__ B2cKArgs a) {
+  constexpr int VW = Mode<MODE>::VW;
+  Ctx c = prologue(a);
+  const int W = a.world;
+  void* buf = a.buf[c.rank];
+  const size_t count = a.count;
+  const size_t nvec = (count + VW - 1) / VW;
+  const size_t nvs = (nvec + W - 1) / W;
+  const bool inplace = a.nvls_inplace != 0;
+  const bool fast = ((reinterpret_cast<uintptr_t>(buf) & 15u) == 0);
+  const size_t base = inplace ? a.nvls_off : (size_t)(c.calls & 1u) * a.nvls_slot_bytes;
+  char* uc = a.nvls_uc + base;
+  char* mc = a.nvls_mc + base;
+
+  if (!inplace) {
+    for (int r = 0; r < W; ++r) {
+      const size_t s0 = (size_t)r * nvs;
+      if (s0 >= nvec) break;
+      const size_t sl = (s0 + nvs <= nvec) ? nvs : nvec - s0;
+      B2C_FOR_OWNED(sl, 8, {
+        uint4 v[8];
+        _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = load_user<MODE>(buf, s0 + idx[u], count, fast);
+        _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) st_v4(uc + (s0 + idx[u]) * 16, v[u]);
+      })
+    }
+  }
+  channel_barrier(a, c, c.epoch + 1u);
+  if (!c.dead) {
+    const size_t s0 = (size_t)c.rank * nvs;
+    const size_t sl = (s0 >= nvec) ? 0 : ((s0 + nvs <= nvec) ? nvs : nvec - s0);
+    B2C_FOR_OWNED(sl, 8, {
+      uint4 v[8];
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u])
+        v[u] = (MODE == MODE_F32) ? multimem_ld_reduce_f32(mc + (s0 + idx[u]) * 16) : multimem_ld_reduce_bf16(mc + (s0 + idx[u]) * 16);
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) {
+        const uint4 res = nvls_scale<MODE>(v[u], a.scale);
+        multimem_st_v4(mc + (s0 + idx[u]) * 16, res);
+        if (!inplace) store_user<MODE>(buf, s0 + idx[u], count, fast, res);
+      }
+    })
+  }
+  channel_barrier(a, c, c.epoch + 2u);
+  if (!c.dead && !inplace) {
+    for (int k = 1; k < W; ++k) {
+      int r = c.rank + k; if (r >= W) r -= W;
+      const size_t s0 = (size_t)r * nvs;
+      if (s0 >= nvec) continue;
+      const size_t sl = (s0 + nvs <= nvec) ? nvs : nvec - s0;
+      B2C_FOR_OWNED(sl, 8, {
+        uint4 v[8];
+        _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = ld_sys_v4(uc + (s0 + idx[u]) * 16);
+        _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) store_user<MODE>(buf, s0 + idx[u], count, fast, v[u]);
+      })
+    }
+  }
   epilogue(c);
 }

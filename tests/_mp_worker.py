@@ -112,6 +112,56 @@ def main():
 
     comm.set_param(_lib.PARAM_ZEROCOPY, 1)
     comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, 0)
+    # ---- NVLS (in-switch reduction) when the box supports NVLink multicast
+    nvls = comm.enable_nvls(64 << 20)
+    if rank == 0:
+        print(f"NVLS enabled={nvls} err={comm.nvls_error}")
+    if nvls:
+        from ray_lightning_accelerators_b200.comm import ALGO_NVLS
+        for kind in ("int", "randn"):
+            for n in (1, 5, 1000, 27882, 3103747):
+                grads = [O.payload(kind, n, r) for r in range(world)]
+                ref = torch.from_numpy(grads[rank]).to(dev).div_(world)
+                dist.all_reduce(ref)
+                denom = sum(np.abs(x.astype(np.float64)) for x in grads) / world
+                for inplace in (False, True):
+                    if inplace:
+                        t = comm.nvls_empty(n)
+                        t.copy_(torch.from_numpy(grads[rank]))
+                    else:
+                        t = torch.from_numpy(grads[rank]).to(dev)
+                    z0 = comm.stats()["nvls_launches"]
+                    comm.allreduce(t, algo=ALGO_NVLS)
+                    torch.cuda.synchronize()
+                    comm.check_alive()
+                    assert comm.stats()["nvls_launches"] > z0
+                    got = t.cpu().numpy()
+                    if kind == "int" and world in (2, 4, 8):
+                        assert torch.equal(bits(t), bits(ref)), ("nvls int bit-exact", n, inplace)
+                    else:
+                        assert O.rel_err(got, ref.cpu().numpy(), denom) <= 1e-6, ("nvls 1e-6", kind, n, inplace)
+                    t0 = t.clone()
+                    dist.broadcast(t0, src=0)
+                    assert torch.equal(bits(t0), bits(t)), "nvls replicas differ"
+        gb = [O.to_bf16_bits(O.payload("randn", 1 << 20, r)) for r in range(world)]
+        t = torch.from_numpy(gb[rank].view(np.int16).copy()).to(dev).view(torch.bfloat16)
+        comm.allreduce(t, algo=ALGO_NVLS)
+        torch.cuda.synchronize()
+        exact = O.exact_mean_bf16_f64(gb)
+        denom = sum(np.abs(O.from_bf16_bits(b).astype(np.float64)) for b in gb) / world
+        assert O.rel_err(O.from_bf16_bits(t.view(torch.int16).cpu().numpy().view(np.uint16)), exact, denom) <= 2.0 ** -8
+        # stress: back-to-back NVLS calls interleaved with the other algorithms
+        outs2 = []
+        for i in range(60):
+            n = 4096 + 1013 * (i % 17)
+            t = torch.full((n,), float(rank + i), device=dev)
+            comm.allreduce(t, algo=ALGO_NVLS if i % 2 == 0 else ALGO_TWOSHOT)
+            outs2.append((t, sum(r + i for r in range(world)) / world))
+        torch.cuda.synchronize()
+        comm.check_alive()
+        for t, want in outs2:
+            assert torch.allclose(t, torch.full_like(t, want), rtol=1e-6, atol=0), "nvls stress"
+    comm.set_param(_lib.PARAM_NVLS_MIN_BYTES, 0)  # the DDP parity section below pins the rank-order contract
     # ---- DDP: our hook vs stock NCCL DDP, MLP (config #2) 100 steps, loss within 1e-5 relative
     def train(use_b2c):
         model = workloads.build_model("mnist_mlp", seed=0).to(dev)

@@ -19,7 +19,7 @@ import torch.distributed as dist
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from ray_lightning_accelerators_b200 import _lib  # noqa: E402
-from ray_lightning_accelerators_b200.comm import ALGO_ONESHOT, ALGO_TWOSHOT, Comm  # noqa: E402
+from ray_lightning_accelerators_b200.comm import ALGO_NVLS, ALGO_ONESHOT, ALGO_TWOSHOT, Comm  # noqa: E402
 
 REAL_BUCKETS = [111528, 1625000, 12415000, 27021000, 29664000, 31500000, 93760000]
 
@@ -52,6 +52,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--max-bytes", type=int, default=1 << 30)
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--fast", action="store_true", help="only one-shot, zero-copy two-shot and NVLS")
+    ap.add_argument("--nvls", action="store_true")
     ap.add_argument("--blocks", default="32,64,128")
     args = ap.parse_args()
 
@@ -61,11 +63,16 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     comm = Comm.from_process_group(arena_bytes=2 * args.max_bytes + (1 << 20))
     comm.set_param(_lib.PARAM_TIMEOUT_MS, 5000)
+    comm.set_param(_lib.PARAM_NVLS_MIN_BYTES, 0)
+    nvls = comm.enable_nvls(2 * args.max_bytes + (4 << 20)) if args.nvls else False
+    if rank == 0:
+        print("NVLS", nvls, comm.nvls_error, flush=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     sizes = sorted(set([1 << k for k in range(10, 31, 2 if args.quick else 1)] + REAL_BUCKETS))
     sizes = [s for s in sizes if s <= args.max_bytes]
     block_opts = [int(b) for b in args.blocks.split(",")]
     rows = []
+    nvls_bufs = {}
     for dtype in (torch.float32, torch.bfloat16):
         for S in sizes:
             es = 4 if dtype == torch.float32 else 2
@@ -87,7 +94,12 @@ def main():
             if rank == 0:
                 print(rows[-1], flush=True)
             configs = []
-            for algo, variant in ((ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1), (ALGO_TWOSHOT, 2)):
+            algos = [(ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 0), (ALGO_TWOSHOT, 1), (ALGO_TWOSHOT, 2)]
+            if args.fast:
+                algos = [(ALGO_ONESHOT, 0), (ALGO_TWOSHOT, 2)]
+            if nvls:
+                algos += [(ALGO_NVLS, 3), (ALGO_NVLS, 4)]  # 3 = staged through the multicast arena, 4 = in place in it
+            for algo, variant in algos:
                 if algo == ALGO_ONESHOT and S > (64 << 20):
                     continue
                 for nb in block_opts:
@@ -99,8 +111,15 @@ def main():
                 comm.set_param(_lib.PARAM_ZEROCOPY, 1 if variant == 2 else 0)  # 2 = in place on registered buffers
                 comm.set_param(_lib.PARAM_MAX_BLOCKS_ONESHOT, nb)
                 comm.set_param(_lib.PARAM_MAX_BLOCKS_TWOSHOT, nb)
+                comm.set_param(_lib.PARAM_MAX_BLOCKS_NVLS, nb)
                 # parity first (same run): vs NCCL and bitwise across replicas
-                y = x.clone()
+                if variant == 4:
+                    if dtype not in nvls_bufs or nvls_bufs[dtype][0].numel() < n:
+                        nvls_bufs[dtype] = (comm.nvls_empty(args.max_bytes // es, dtype), comm.nvls_empty(args.max_bytes // es, dtype))
+                    y = nvls_bufs[dtype][0][:n]
+                    y.copy_(x)
+                else:
+                    y = x.clone()
                 if variant == 2:
                     comm.register(y)
                 comm.allreduce(y, algo=algo)
@@ -116,7 +135,11 @@ def main():
                                         y.view(torch.int16 if es == 2 else torch.int32)))
                 bitexact = bool(torch.equal(y.view(torch.int16 if es == 2 else torch.int32),
                                             ref.view(torch.int16 if es == 2 else torch.int32)))
-                buf = x.clone()
+                if variant == 4:
+                    buf = nvls_bufs[dtype][1][:n]
+                    buf.copy_(x)
+                else:
+                    buf = x.clone()
                 if variant == 2:
                     comm.register(buf)
 
@@ -126,7 +149,7 @@ def main():
                 med, p99, mean = timed(b2c_fn, comm, flush, args.iters, args.warmup)
                 st = comm.stats()
                 rows.append(dict(impl="b2c", W=world, dtype=str(dtype).split(".")[1], bytes=S,
-                                 algo={1: "oneshot", 2: "twoshot"}[algo], variant=variant, zerocopy=(variant == 2),
+                                 algo={1: "oneshot", 2: "twoshot", 3: "nvls"}[algo], variant=variant, zerocopy=(variant == 2),
                                  max_blocks=nb,
                                  blocks=st["last_blocks"], us_med=med, us_p99=p99, us_mean=mean,
                                  busbw_GBps=busf / med / 1e3, rel_err_vs_nccl=err, within_tol=bool(err <= tol),
