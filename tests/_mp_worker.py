@@ -149,7 +149,12 @@ def main():
         torch.cuda.synchronize()
         exact = O.exact_mean_bf16_f64(gb)
         denom = sum(np.abs(O.from_bf16_bits(b).astype(np.float64)) for b in gb) / world
-        assert O.rel_err(O.from_bf16_bits(t.view(torch.int16).cpu().numpy().view(np.uint16)), exact, denom) <= 2.0 ** -8
+        got_bits = t.view(torch.int16).cpu().numpy().view(np.uint16)
+        err = O.rel_err(O.from_bf16_bits(got_bits), exact, denom)
+        want_bits = O.b2c_allreduce_bf16(gb)
+        nbad = int((O.bf16_ulp_diff(got_bits, want_bits) > 1).sum())
+        # the switch's bf16 result is not always the correctly rounded one: bar = north_star's "one bf16 ulp"
+        assert nbad == 0 and err <= 2.0 ** -7, f"nvls bf16: rel err {err}, {nbad} elements more than 1 ulp from the contract"
         # stress: back-to-back NVLS calls interleaved with the other algorithms
         outs2 = []
         for i in range(60):

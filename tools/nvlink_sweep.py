@@ -114,8 +114,9 @@ def main():
                 comm.set_param(_lib.PARAM_MAX_BLOCKS_NVLS, nb)
                 # parity first (same run): vs NCCL and bitwise across replicas
                 if variant == 4:
-                    if dtype not in nvls_bufs or nvls_bufs[dtype][0].numel() < n:
-                        nvls_bufs[dtype] = (comm.nvls_empty(args.max_bytes // es, dtype), comm.nvls_empty(args.max_bytes // es, dtype))
+                    if not nvls_bufs:
+                        nvls_bufs["raw"] = (comm.nvls_empty(args.max_bytes, torch.uint8), comm.nvls_empty(args.max_bytes, torch.uint8))
+                    nvls_bufs[dtype] = tuple(r.view(dtype) for r in nvls_bufs["raw"])
                     y = nvls_bufs[dtype][0][:n]
                     y.copy_(x)
                 else:
