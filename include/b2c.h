@@ -197,6 +197,29 @@ int b2c_nvls_import(b2c_comm* comm, const void* blobs, size_t len_each);
 int b2c_nvls_bind(b2c_comm* comm);
 int b2c_nvls_arena(b2c_comm* comm, void** base, size_t* bytes);
 
+/* ---- allocation-free variant ----------------------------------------------
+ * No counterpart in the reference.
+ * b2c_allreduce_local_noalloc: the one-shot allreduce of a single-device group
+ * (b2c_group_allreduce with B2C_ALGO_ONESHOT), for callers that must not allocate device
+ * memory where they need the reduction: code that runs after the training framework's
+ * caching allocator has claimed the GPU (a cudaMalloc there can fail, or make the framework
+ * flush its cache), and code on the autograd hook thread in the middle of backward, where a
+ * cudaMalloc / cudaFree would synchronise the whole device and stall the overlapped step.
+ * It needs no b2c_comm: flags and staging slots live in a file-scope device array inside
+ * libb2c.so (about 2.1 MiB, held by every GPU that loads the library until the process
+ * exits).  bufs[r] (r < world <= 8) are `count` elements of `dtype` (B2C_F32 or B2C_BF16) on
+ * the CURRENT device; each ends up holding sum_r bufs[r] * scale, same arithmetic contract
+ * as b2c_allreduce.  Limit: count * element size <= B2C_NOALLOC_MAX_BYTES per buffer;
+ * anything larger is refused with B2C_ETOOBIG.  The call enqueues a few small memsets (the
+ * flag / counter words are cleared every time, because the array keeps whatever the last
+ * call left) and one cooperative kernel on `stream`, and calls no allocating routine.
+ * The first call on a device looks up the array's device address; make that first call
+ * before starting any stream capture.  All calls on a device share the one array: two calls
+ * that can overlap on the GPU (different streams, no dependency) race with each other. */
+#define B2C_NOALLOC_MAX_BYTES (256 * 1024)
+int b2c_allreduce_local_noalloc(void* const* bufs, int world, size_t count, int dtype, float scale,
+                                b2c_stream_t stream);
+
 /* ---- knobs, counters, introspection ------------------------------------ */
 int b2c_set_param(b2c_comm* comm, int key, long value);
 int b2c_get_param(b2c_comm* comm, int key, long* value);

@@ -30,6 +30,7 @@ PARAM_NVLS_MIN_BYTES = 9
 PARAM_MAX_BLOCKS_NVLS = 10
 REG_BLOB_BYTES = 128
 NVLS_BLOB_BYTES = 64
+NOALLOC_MAX_BYTES = 256 * 1024
 MAX_WORLD = 8
 MAX_BLOCKS = 256
 EXPORT_BLOB_BYTES = 256
@@ -101,6 +102,7 @@ SIGNATURES = {
     "b2c_nvls_import": (_int, [_vp, _vp, _sz]),
     "b2c_nvls_bind": (_int, [_vp]),
     "b2c_nvls_arena": (_int, [_vp, _pp, _c.POINTER(_sz)]),
+    "b2c_allreduce_local_noalloc": (_int, [_pp, _int, _sz, _int, _c.c_float, _vp]),
     "b2c_set_param": (_int, [_vp, _int, _c.c_long]),
     "b2c_get_param": (_int, [_vp, _int, _c.POINTER(_c.c_long)]),
     "b2c_get_stats": (_int, [_vp, _c.POINTER(Stats)]),

@@ -7,6 +7,7 @@
 #include <unistd.h>
 #include <sys/syscall.h>
 #include <errno.h>
+#include <pthread.h>
 #include <cuda.h>   // types only: the driver API is reached through cudaGetDriverEntryPoint (no -lcuda)
 
 #include "b2c_kernels.cuh"
@@ -883,6 +884,106 @@ extern "C" int b2c_nvls_arena(b2c_comm* c, void** base, size_t* bytes) {
   if (!c->nvls || c->nvls->phase != 3) return fail(B2C_ESTATE, "b2c_nvls_arena: multicast arena is not set up");
   if (base) *base = (void*)c->nvls->uc;
   if (bytes) *bytes = c->nvls->bytes;
+  return B2C_OK;
+}
+
+// ---------------------------------------------------------------- allocation-free local allreduce
+// For callers that cannot allocate where they need the reduction (see include/b2c.h): the
+// scratch a local group normally gets from cudaMalloc — control words, flag page and one staging
+// slot per virtual rank — lives in this file-scope device array instead.  Every GPU that loads
+// the library carries it (B2C_MAX_WORLD x (16 KiB header + 256 KiB slot) = 2,228,224 bytes).
+#define B2C_NOALLOC_REGION_BYTES (B2C_HEADER_BYTES + B2C_NOALLOC_MAX_BYTES)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B2C_MAX_WORLD * B2C_NOALLOC_REGION_BYTES];
+
+#define B2C_NOALLOC_MAX_DEVICES 64
+static pthread_mutex_t g_noalloc_lock = PTHREAD_MUTEX_INITIALIZER;
+static char* g_noalloc_addr[B2C_NOALLOC_MAX_DEVICES];   // per device: where the array lives ON that device
+static int g_noalloc_blocks[B2C_NOALLOC_MAX_DEVICES];   // per device: co-resident CTAs of the widest kernel
+
+// Once per device, with that device current.  In host code `g_noalloc_scratch` is only a handle for
+// the runtime, not a device address: the address has to be asked for, per device.
+static int noalloc_setup(int dev, char** base, int* resident) {
+  if (dev < 0 || dev >= B2C_NOALLOC_MAX_DEVICES) return fail(B2C_EINVAL, "b2c_allreduce_local_noalloc: device %d out of range", dev);
+  pthread_mutex_lock(&g_noalloc_lock);
+  int rc = B2C_OK;
+  if (!g_noalloc_addr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    int per_sm = 0, sms = 0;
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_allreduce_oneshot<MODE_F32, B2C_MAX_WORLD>, 512, 0);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      rc = cuda_fail(e, "b2c_allreduce_local_noalloc: set-up (cudaGetSymbolAddress / occupancy)");
+    } else {
+      g_noalloc_blocks[dev] = per_sm * sms;
+      g_noalloc_addr[dev] = (char*)p;
+    }
+  }
+  *base = g_noalloc_addr[dev];
+  *resident = g_noalloc_blocks[dev];
+  pthread_mutex_unlock(&g_noalloc_lock);
+  return rc;
+}
+
+extern "C" int b2c_allreduce_local_noalloc(void* const* bufs, int world, size_t count, int dtype, float scale,
+                                           b2c_stream_t stream) {
+  if (!bufs) return fail(B2C_EINVAL, "b2c_allreduce_local_noalloc: bufs is NULL");
+  if (world < 1 || world > B2C_MAX_WORLD) return fail(B2C_EINVAL, "b2c_allreduce_local_noalloc: world=%d outside 1..%d", world, B2C_MAX_WORLD);
+  int mode, vw, ub;
+  if (dtype != B2C_F32 && dtype != B2C_BF16) return fail(B2C_EUNSUPPORTED, "b2c_allreduce_local_noalloc: dtype=%d (B2C_F32 or B2C_BF16)", dtype);
+  int rc = mode_of(dtype, dtype, &mode, &vw, &ub);
+  if (rc) return rc;
+  if (count > (size_t)B2C_NOALLOC_MAX_BYTES / ub)
+    return fail(B2C_ETOOBIG, "b2c_allreduce_local_noalloc: %zu elements x %d bytes exceed the built-in scratch of %d bytes per buffer; "
+                "use b2c_group_allreduce (which allocates an arena) for larger buffers", count, ub, (int)B2C_NOALLOC_MAX_BYTES);
+  for (int r = 0; r < world; ++r) {
+    if (!bufs[r]) return fail(B2C_EINVAL, "b2c_allreduce_local_noalloc: bufs[%d] is NULL", r);
+    if ((uintptr_t)bufs[r] % ub) return fail(B2C_EINVAL, "b2c_allreduce_local_noalloc: bufs[%d] is not aligned to its element size", r);
+  }
+  if (count == 0) return B2C_OK;
+  int dev = -1;
+  CU(cudaGetDevice(&dev));
+  char* base = nullptr;
+  int resident = 0;
+  rc = noalloc_setup(dev, &base, &resident);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+
+  Launch L;
+  memset(&L.args, 0, sizeof(L.args));
+  for (int q = 0; q < world; ++q) {
+    char* region = base + (size_t)q * B2C_NOALLOC_REGION_BYTES;
+    // the array remembers the previous call (which may have had another world size): epochs,
+    // call counter, exit ticket, error words and flags all have to start from zero
+    CU(cudaMemsetAsync(region, 0, B2C_CTL_BYTES + B2C_FLAG_BYTES, st));
+    L.args.region[q] = region;
+    L.args.status[q] = reinterpret_cast<uint32_t*>(region + 1024);  // inside the cleared control page
+    L.args.buf[q] = bufs[q];
+  }
+  L.args.count = count;
+  L.args.slot_bytes = B2C_NOALLOC_MAX_BYTES;
+  L.args.timeout_ns = 2000ull * 1000000ull;
+  L.args.scale = scale;
+  L.args.rank = -1;  // one cooperative launch runs every virtual rank (grid.y = world)
+  L.args.world = world;
+  L.fn = mode == MODE_F32 ? oneshot_fn<MODE_F32>(world) : oneshot_fn<MODE_BF16>(world);
+  const size_t nvec = (count + vw - 1) / vw;
+  long cap = resident / world;
+  if (cap > 32) cap = 32;
+  if (cap < 1) cap = 1;
+  size_t nb = (nvec + 511) / 512;
+  if (nb > (size_t)cap) nb = cap;
+  if (nb < 1) nb = 1;
+  size_t cu = (nvec + 512 * nb - 1) / (512 * nb);  // <= 4 here: 16384 vectors at most
+  L.nblocks = (int)nb;
+  L.threads = 512;
+  L.args.chunk_vecs = (uint32_t)(512 * (cu < 1 ? 1 : cu));
+  void* params[] = {(void*)&L.args};
+  dim3 grid(L.nblocks, world), block(L.threads);
+  cudaError_t e = (world > 1) ? cudaLaunchCooperativeKernel(L.fn, grid, block, params, 0, st)
+                              : cudaLaunchKernel(L.fn, grid, block, params, 0, st);
+  if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, "b2c_allreduce_local_noalloc: kernel launch"); }
   return B2C_OK;
 }
 
