@@ -207,7 +207,8 @@ def run_b2c(args):
     if rank == 0:
         sampler.start()
     state.enable_timing()
-    launches0 = comm.stats()["launches"]
+    st0 = comm.stats()
+    launches0 = st0["launches"]
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -219,7 +220,16 @@ def run_b2c(args):
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     clocks = sampler.stop() if rank == 0 else None
-    launches = comm.stats()["launches"] - launches0
+    st1 = comm.stats()
+    launches = st1["launches"] - launches0
+    if st1["nvls_launches"] > st0["nvls_launches"]:
+        grad_kernel, grad_path = "k_allreduce_nvls<f32>", "libb2c.so: NVLS in-switch reduction, DDP buckets inside the multicast arena (in place)"
+    elif st1["zerocopy_launches"] > st0["zerocopy_launches"]:
+        grad_kernel, grad_path = f"k_allreduce_twoshot_zc<f32,W={world}>", "libb2c.so: zero-copy two-shot on registered DDP buckets"
+    elif world > 1:
+        grad_kernel, grad_path = f"k_allreduce_twoshot<f32,W={world}>", "libb2c.so: staged two-shot / one-shot through the arena"
+    else:
+        grad_kernel, grad_path = "k_allreduce_oneshot<f32,W=1>", "libb2c.so: W=1 scale pass (no peer)"
     per_bucket_us, n_timed = _bucket_stats(state)
     state.timing = None
     ms_total = float(ms.item())
@@ -268,7 +278,7 @@ def run_b2c(args):
                         "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom}
         else:
             alg = 2.0 * (world - 1) / world * dom  # NVLink bytes per GPU per direction (busbw numerator)
-            roofline = {"bound": "nvlink", "kernel": f"k_allreduce_twoshot_zc<f32,W={world}>",
+            roofline = {"bound": "nvlink", "kernel": grad_kernel,
                         "achieved": alg / us / 1e3, "peak": NVLINK_NOMINAL_GBPS,
                         "peak_kind": "nominal NVLink 5 per direction (measured peer copy 770 GB/s)", "unit": "GB/s",
                         "frac": alg / us / 1e3 / NVLINK_NOMINAL_GBPS,
@@ -291,8 +301,7 @@ def run_b2c(args):
                                    f"buckets via RayAccelerator(use_gpu=True) plugin methods (BASELINE configs[2])",
                        "global_batch": batch * world, "parallelism": f"dp{world}",
                        "l2": "inputs larger than L2 (activations of a 256-image batch >> 126 MB); no flush needed",
-                       "grad_path": "libb2c.so: zero-copy two-shot on registered DDP buckets" if world > 1
-                                    else "libb2c.so: W=1 scale pass (no peer)"},
+                       "grad_path": grad_path},
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": float(ms2.item()) / K, "last_loss": last},
             "gpu_launches": int(launches), "b2c_launches_timed": int(n_timed),
@@ -342,13 +351,22 @@ def _allreduce_section(args, comm, rank, world, dev):
 
     if world > 1:
         for S in RESNET50_BUCKETS:
-            x = torch.randn(S // 4, device=dev)
-            comm.register(x)
+            if comm.nvls_enabled:
+                try:
+                    x = comm.nvls_empty(S // 4)   # lives in the multicast arena: in-switch reduction, in place
+                    x.normal_()
+                except MemoryError:
+                    x = torch.randn(S // 4, device=dev)
+            else:
+                x = torch.randn(S // 4, device=dev)
+            if not comm.in_nvls_arena(x):
+                comm.register(x)
             us = timed(lambda: comm.allreduce(x, algo=ALGO_AUTO), comm.barrier)
+            path = {1: "oneshot", 2: "twoshot", 3: "nvls"}[comm.stats()["last_algo"]]
             y = torch.randn(S // 4, device=dev)
             us_nccl = timed(lambda: dist.all_reduce(y), comm.barrier)
             bus = 2.0 * (world - 1) / world * S
-            out.append({"bytes": S, "us": us, "busbw_GBps": bus / us / 1e3, "frac_of_900": bus / us / 1e3 / NVLINK_NOMINAL_GBPS,
+            out.append({"bytes": S, "path": path, "us": us, "busbw_GBps": bus / us / 1e3, "frac_of_900": bus / us / 1e3 / NVLINK_NOMINAL_GBPS,
                         "nccl_us": us_nccl, "nccl_busbw_GBps": bus / us_nccl / 1e3})
         return {"mode": f"nvlink W={world}", "timing": "median of %d, L2 flushed, max over ranks" % iters, "buckets": out}
     g = LocalGroup(8, device=dev.index or 0, arena_bytes=8 << 20)

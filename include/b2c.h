@@ -69,7 +69,9 @@ enum {
   B2C_PARAM_NVLS_MIN_BYTES = 9,   /* AUTO: wire bytes at or above which the NVLS path is used when
                                      the multicast arena is up (0 = never pick it automatically) */
   B2C_PARAM_MAX_BLOCKS_NVLS = 10,
-  B2C_PARAM__COUNT = 11
+  B2C_PARAM_UNROLL_NVLS = 11,     /* multimem.ld_reduce vectors in flight per thread: 2, 4, 8 or 16 */
+  B2C_PARAM_UNROLL_ZC = 12,       /* zero-copy two-shot, W = 8 only: 0 (default 2), 1, 2 or 4 vectors per peer in flight */
+  B2C_PARAM__COUNT = 13
 };
 
 /* error codes */
@@ -196,6 +198,16 @@ int b2c_nvls_export(b2c_comm* comm, size_t bytes, void* blob, size_t* len);
 int b2c_nvls_import(b2c_comm* comm, const void* blobs, size_t len_each);
 int b2c_nvls_bind(b2c_comm* comm);
 int b2c_nvls_arena(b2c_comm* comm, void** base, size_t* bytes);
+/* Bump allocation inside the arena (256-byte aligned, same sequence on every rank => same offsets).
+ * b2c_nvls_pool_bind makes this comm's arena the backing store of b2c_pool_alloc / b2c_pool_free,
+ * which have the signature torch.cuda.memory.CUDAPluggableAllocator expects: DDP built inside a
+ * torch.cuda.MemPool on that allocator gets its gradient buckets INSIDE the multicast arena, so the
+ * per-step allreduce is the in-place NVLS kernel with no staging at all.  Frees are LIFO roll-backs
+ * or no-ops (the buckets live as long as the comm). */
+int b2c_nvls_alloc(b2c_comm* comm, size_t bytes, void** ptr);
+int b2c_nvls_pool_bind(b2c_comm* comm);
+void* b2c_pool_alloc(ptrdiff_t size, int device, b2c_stream_t stream);
+void b2c_pool_free(void* ptr, ptrdiff_t size, int device, b2c_stream_t stream);
 
 /* ---- allocation-free variant ----------------------------------------------
  * No counterpart in the reference.

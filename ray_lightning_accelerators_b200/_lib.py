@@ -28,6 +28,8 @@ PARAM_ZEROCOPY = 7
 PARAM_ZEROCOPY_MIN_BYTES = 8
 PARAM_NVLS_MIN_BYTES = 9
 PARAM_MAX_BLOCKS_NVLS = 10
+PARAM_UNROLL_NVLS = 11
+PARAM_UNROLL_ZC = 12
 REG_BLOB_BYTES = 128
 NVLS_BLOB_BYTES = 64
 NOALLOC_MAX_BYTES = 256 * 1024
@@ -102,6 +104,10 @@ SIGNATURES = {
     "b2c_nvls_import": (_int, [_vp, _vp, _sz]),
     "b2c_nvls_bind": (_int, [_vp]),
     "b2c_nvls_arena": (_int, [_vp, _pp, _c.POINTER(_sz)]),
+    "b2c_nvls_alloc": (_int, [_vp, _sz, _pp]),
+    "b2c_nvls_pool_bind": (_int, [_vp]),
+    "b2c_pool_alloc": (_vp, [_c.c_ssize_t, _int, _vp]),
+    "b2c_pool_free": (None, [_vp, _c.c_ssize_t, _int, _vp]),
     "b2c_allreduce_local_noalloc": (_int, [_pp, _int, _sz, _int, _c.c_float, _vp]),
     "b2c_set_param": (_int, [_vp, _int, _c.c_long]),
     "b2c_get_param": (_int, [_vp, _int, _c.POINTER(_c.c_long)]),

@@ -202,10 +202,11 @@ class Comm(_Base):
             raise RuntimeError("multicast arena is not set up (enable_nvls)")
         es = torch.empty(0, dtype=dtype).element_size()
         nbytes = (numel * es + 255) // 256 * 256
-        if self._nvls_top + nbytes > self._nvls_bytes:
-            raise MemoryError(f"multicast arena exhausted ({self._nvls_bytes} bytes)")
-        ptr = self._nvls_base + self._nvls_top
-        self._nvls_top += nbytes
+        p = ctypes.c_void_p()
+        rc = self._lib.b2c_nvls_alloc(self._h, nbytes, ctypes.byref(p))
+        if rc != 0:
+            raise MemoryError(_lib.last_error())
+        ptr = p.value
 
         class _Raw:  # __cuda_array_interface__ v3: zero-copy view of raw device memory
             pass
@@ -215,6 +216,25 @@ class Comm(_Base):
                                         "strides": None}
         flat = torch.as_tensor(raw, device=torch.device("cuda", self.device))
         return flat[:numel * es].view(dtype)
+
+    def torch_pool(self):
+        """A torch.cuda.MemPool whose segments come out of the multicast arena: tensors allocated
+        under `torch.cuda.use_mem_pool(pool)` (DDP's gradient buckets, when DDP is constructed
+        there) are reduced in place by the NVLS kernel.  One pool per process."""
+        if not self._nvls:
+            raise RuntimeError("multicast arena is not set up (enable_nvls)")
+        if getattr(self, "_pool", None) is None:
+            _lib.check(self._lib.b2c_nvls_pool_bind(self._h))
+            self._pool_alloc = torch.cuda.memory.CUDAPluggableAllocator(_lib.LIB_PATH, "b2c_pool_alloc", "b2c_pool_free")
+            self._pool = torch.cuda.MemPool(self._pool_alloc.allocator())
+        return self._pool
+
+    def in_nvls_arena(self, t):
+        return self._nvls and self._nvls_base <= t.data_ptr() < self._nvls_base + self._nvls_bytes
+
+    @property
+    def nvls_enabled(self):
+        return self._nvls
 
     def deregister(self, t):
         key = (t.data_ptr(), t.numel() * t.element_size())

@@ -92,6 +92,7 @@ struct Nvls {
   int mc_fd;                              // rank 0: exported fd of the multicast object
   CUdeviceptr uc, mcva;
   bool uc_mapped, mc_mapped, bound;
+  size_t top, last;                       // bump allocator inside the arena
 };
 struct Registration {
   char* local;                       // caller pointer on this rank
@@ -117,6 +118,8 @@ struct RegBlob {
 static_assert(sizeof(RegBlob) <= B2C_REG_BLOB_BYTES, "reg blob too large");
 
 static void nvls_release(b2c_comm* c);
+static pthread_mutex_t g_pool_lock = PTHREAD_MUTEX_INITIALIZER;
+static b2c_comm* g_pool_comm = nullptr;  // whose multicast arena backs b2c_pool_alloc / b2c_pool_free
 
 static uint64_t host_identity() {
   uint64_t h = (uint64_t)gethostid();
@@ -140,8 +143,10 @@ static void default_params(b2c_comm* c) {
   c->params[B2C_PARAM_MAX_BLOCKS_BCAST] = 32;
   c->params[B2C_PARAM_ZEROCOPY] = 1;
   c->params[B2C_PARAM_ZEROCOPY_MIN_BYTES] = 256 * 1024;
-  c->params[B2C_PARAM_NVLS_MIN_BYTES] = 2 * 1024 * 1024;
-  c->params[B2C_PARAM_MAX_BLOCKS_NVLS] = 64;
+  c->params[B2C_PARAM_NVLS_MIN_BYTES] = 64 * 1024;
+  c->params[B2C_PARAM_MAX_BLOCKS_NVLS] = 8;   // the switch saturates with 4-8 CTAs; more only adds congestion
+  c->params[B2C_PARAM_UNROLL_NVLS] = 8;
+  c->params[B2C_PARAM_UNROLL_ZC] = 0;
 }
 
 static int comm_alloc(int rank, int world, int device, size_t arena_bytes, b2c_comm** out) {
@@ -347,6 +352,37 @@ template <int MODE> static const void* twoshot_zc_fn(int W) {
   }
 }
 
+static const void* nvls_fn(int mode, int unroll) {
+  if (mode == MODE_F32) {
+    switch (unroll) {
+      case 2: return (const void*)k_allreduce_nvls<MODE_F32, 2>;
+      case 4: return (const void*)k_allreduce_nvls<MODE_F32, 4>;
+      case 16: return (const void*)k_allreduce_nvls<MODE_F32, 16>;
+      default: return (const void*)k_allreduce_nvls<MODE_F32, 8>;
+    }
+  }
+  switch (unroll) {
+    case 2: return (const void*)k_allreduce_nvls<MODE_BF16, 2>;
+    case 4: return (const void*)k_allreduce_nvls<MODE_BF16, 4>;
+    case 16: return (const void*)k_allreduce_nvls<MODE_BF16, 16>;
+    default: return (const void*)k_allreduce_nvls<MODE_BF16, 8>;
+  }
+}
+static const void* zc8_fn(int mode, int unroll) {
+  if (mode == MODE_F32) {
+    switch (unroll) {
+      case 1: return (const void*)k_allreduce_twoshot_zc<MODE_F32, 8, 1>;
+      case 4: return (const void*)k_allreduce_twoshot_zc<MODE_F32, 8, 4>;
+      default: return (const void*)k_allreduce_twoshot_zc<MODE_F32, 8, 2>;
+    }
+  }
+  switch (unroll) {
+    case 1: return (const void*)k_allreduce_twoshot_zc<MODE_BF16, 8, 1>;
+    case 4: return (const void*)k_allreduce_twoshot_zc<MODE_BF16, 8, 4>;
+    default: return (const void*)k_allreduce_twoshot_zc<MODE_BF16, 8, 2>;
+  }
+}
+
 // registration covering [p, p+bytes), or NULL
 static Registration* find_reg(b2c_comm* c, const void* p, size_t bytes) {
   const char* q = (const char*)p;
@@ -489,12 +525,19 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
   const bool nvls_up = !group && c->nvls && c->nvls->phase == 3;
   if (algo == B2C_ALGO_NVLS && !nvls_up)
     return fail(B2C_ESTATE, "b2c_allreduce: algo NVLS requested but the multicast arena is not set up (b2c_nvls_export/import/bind)");
+  bool nvls_inside = false;
+  if (nvls_up) {
+    char* p0 = (char*)bufs[c->rank];
+    nvls_inside = p0 >= (char*)c->nvls->uc && p0 + count * ub <= (char*)c->nvls->uc + c->nvls->bytes && (((uintptr_t)p0 & 15u) == 0);
+  }
+  // AUTO takes the switch only for tensors that live in the arena (in place); staging through the
+  // arena loses to the zero-copy peer path and is only run on explicit request
   if (nvls_up && W > 1 && mode != MODE_F32_BF16 &&
-      (algo == B2C_ALGO_NVLS || (algo == B2C_ALGO_AUTO && c->params[B2C_PARAM_NVLS_MIN_BYTES] > 0 &&
+      (algo == B2C_ALGO_NVLS || (algo == B2C_ALGO_AUTO && nvls_inside && c->params[B2C_PARAM_NVLS_MIN_BYTES] > 0 &&
                                  count * (size_t)ub >= (size_t)c->params[B2C_PARAM_NVLS_MIN_BYTES]))) {
     Nvls* nv = c->nvls;
     char* p = (char*)bufs[c->rank];
-    const bool inside = p >= (char*)nv->uc && p + count * ub <= (char*)nv->uc + nv->bytes && (((uintptr_t)p & 15u) == 0);
+    const bool inside = nvls_inside;
     const size_t piece = inside ? count : (nv->slot_bytes / 16) * vw;
     for (size_t off = 0; off < count; off += piece) {
       const size_t n = (count - off < piece) ? count - off : piece;
@@ -509,7 +552,7 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
       L.args.nvls_inplace = inside ? 1 : 0;
       L.args.nvls_off = inside ? (size_t)(p - (char*)nv->uc) : 0;
       const size_t nvec = (n + vw - 1) / vw;
-      L.fn = mode == MODE_F32 ? (const void*)k_allreduce_nvls<MODE_F32> : (const void*)k_allreduce_nvls<MODE_BF16>;
+      L.fn = nvls_fn(mode, (int)c->params[B2C_PARAM_UNROLL_NVLS]);
       geometry(c, (nvec + W - 1) / W, c->params[B2C_PARAM_MAX_BLOCKS_NVLS], &L.nblocks, &L.threads, &L.args.chunk_vecs);
       c->stats.nvls_launches++;
       c->stats.last_algo = B2C_ALGO_NVLS;
@@ -539,6 +582,7 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
       L.args.scale = scale;
       const size_t nvs = (count / vw + W - 1) / W;
       L.fn = mode == MODE_F32 ? twoshot_zc_fn<MODE_F32>(W) : twoshot_zc_fn<MODE_BF16>(W);
+      if (W == 8 && c->params[B2C_PARAM_UNROLL_ZC] > 0) L.fn = zc8_fn(mode, (int)c->params[B2C_PARAM_UNROLL_ZC]);
       long mb = c->params[B2C_PARAM_MAX_BLOCKS_TWOSHOT];
       if (group) mb = group_block_cap(c, L.fn, mb);
       geometry(c, nvs, mb, &L.nblocks, &L.threads, &L.args.chunk_vecs);
@@ -550,7 +594,8 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
   }
 
   const size_t slot_vecs = c->slot_bytes / 16;
-  const size_t piece_elems = slot_vecs * vw;  // keeps every piece 16-byte aligned relative to buf
+  // pieces keep 16-byte alignment relative to buf; a single rank never touches the arena, so no split
+  const size_t piece_elems = (W == 1) ? (count > 0 ? count : 1) : slot_vecs * vw;
   for (size_t off = 0; off < count; off += piece_elems) {
     const size_t n = (count - off < piece_elems) ? count - off : piece_elems;
     const size_t nvec = (n + vw - 1) / vw;
@@ -747,6 +792,9 @@ static int drv_fail(Drv* d, CUresult r, const char* what) {
   } while (0)
 
 static void nvls_release(b2c_comm* c) {
+  pthread_mutex_lock(&g_pool_lock);
+  if (g_pool_comm == c) g_pool_comm = nullptr;
+  pthread_mutex_unlock(&g_pool_lock);
   Nvls* n = c->nvls;
   Drv* d = drv();
   if (!n) return;
@@ -885,6 +933,46 @@ extern "C" int b2c_nvls_arena(b2c_comm* c, void** base, size_t* bytes) {
   if (base) *base = (void*)c->nvls->uc;
   if (bytes) *bytes = c->nvls->bytes;
   return B2C_OK;
+}
+
+extern "C" int b2c_nvls_alloc(b2c_comm* c, size_t bytes, void** ptr) {
+  if (!c || !ptr) return fail(B2C_EINVAL, "b2c_nvls_alloc: NULL argument");
+  if (!c->nvls || c->nvls->phase != 3) return fail(B2C_ESTATE, "b2c_nvls_alloc: multicast arena is not set up");
+  Nvls* n = c->nvls;
+  const size_t need = (bytes + 255) & ~(size_t)255;
+  pthread_mutex_lock(&g_pool_lock);
+  int rc = B2C_OK;
+  if (n->top + need > n->bytes) {
+    rc = fail(B2C_ETOOBIG, "b2c_nvls_alloc: %zu bytes do not fit (arena %zu, used %zu)", bytes, n->bytes, n->top);
+  } else {
+    n->last = n->top;
+    *ptr = (void*)(n->uc + n->top);
+    n->top += need;
+  }
+  pthread_mutex_unlock(&g_pool_lock);
+  return rc;
+}
+extern "C" int b2c_nvls_pool_bind(b2c_comm* c) {
+  if (c && (!c->nvls || c->nvls->phase != 3)) return fail(B2C_ESTATE, "b2c_nvls_pool_bind: multicast arena is not set up");
+  pthread_mutex_lock(&g_pool_lock);
+  g_pool_comm = c;
+  pthread_mutex_unlock(&g_pool_lock);
+  return B2C_OK;
+}
+extern "C" void* b2c_pool_alloc(ptrdiff_t size, int device, b2c_stream_t stream) {
+  (void)device; (void)stream;
+  void* p = nullptr;
+  if (!g_pool_comm || size < 0 || b2c_nvls_alloc(g_pool_comm, (size_t)size, &p) != B2C_OK) return nullptr;
+  return p;
+}
+extern "C" void b2c_pool_free(void* ptr, ptrdiff_t size, int device, b2c_stream_t stream) {
+  (void)size; (void)device; (void)stream;
+  pthread_mutex_lock(&g_pool_lock);
+  if (g_pool_comm && g_pool_comm->nvls) {
+    Nvls* n = g_pool_comm->nvls;
+    if ((char*)ptr == (char*)n->uc + n->last) n->top = n->last;  // LIFO roll-back; anything else stays reserved
+  }
+  pthread_mutex_unlock(&g_pool_lock);
 }
 
 // ---------------------------------------------------------------- allocation-free local allreduce
@@ -1117,6 +1205,12 @@ extern "C" int b2c_set_param(b2c_comm* c, int key, long v) {
       break;
     case B2C_PARAM_TWOSHOT_VARIANT:
       if (v != 0 && v != 1) return fail(B2C_EINVAL, "b2c_set_param: twoshot variant %ld (0 = push, 1 = pull)", v);
+      break;
+    case B2C_PARAM_UNROLL_NVLS:
+      if (v != 2 && v != 4 && v != 8 && v != 16) return fail(B2C_EINVAL, "b2c_set_param: nvls unroll %ld (2, 4, 8 or 16)", v);
+      break;
+    case B2C_PARAM_UNROLL_ZC:
+      if (v != 0 && v != 1 && v != 2 && v != 4) return fail(B2C_EINVAL, "b2c_set_param: zero-copy unroll %ld (0, 1, 2 or 4)", v);
       break;
     case B2C_PARAM_ZEROCOPY:
       if (v != 0 && v != 1) return fail(B2C_EINVAL, "b2c_set_param: zerocopy=%ld (0 or 1)", v);

@@ -529,10 +529,10 @@ template <> struct Elem<MODE_BF16> {
   }
 };
 
-template <int MODE, int W>
+template <int MODE, int W, int UU = 0>
 __global__ void __launch_bounds__(512, 1) k_allreduce_twoshot_zc(const __grid_constant__ B2cKArgs a) {
   constexpr int VW = Mode<MODE>::VW;
-  constexpr int U = Unroll<W>::U;
+  constexpr int U = UU > 0 ? UU : Unroll<W>::U;
   Ctx c = prologue(a);
   const size_t count = a.count;
   const size_t nfull = count / VW;          // whole vectors
@@ -616,7 +616,7 @@ __device__ __forceinline__ uint4 nvls_scale(uint4 v, float scale) {
   }
 }
 
-template <int MODE>
+template <int MODE, int NU = 8>
 __global__ void __launch_bounds__(512, 1) k_allreduce_nvls(const __grid_constant__ B2cKArgs a) {
   constexpr int VW = Mode<MODE>::VW;
   Ctx c = prologue(a);
@@ -647,11 +647,11 @@ __global__ void __launch_bounds__(512, 1) k_allreduce_nvls(const __grid_constant
   if (!c.dead) {
     const size_t s0 = (size_t)c.rank * nvs;
     const size_t sl = (s0 >= nvec) ? 0 : ((s0 + nvs <= nvec) ? nvs : nvec - s0);
-    B2C_FOR_OWNED(sl, 8, {
-      uint4 v[8];
-      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u])
+    B2C_FOR_OWNED(sl, NU, {
+      uint4 v[NU];
+      _Pragma("unroll") for (int u = 0; u < NU; ++u) if (pred[u])
         v[u] = (MODE == MODE_F32) ? multimem_ld_reduce_f32(mc + (s0 + idx[u]) * 16) : multimem_ld_reduce_bf16(mc + (s0 + idx[u]) * 16);
-      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) {
+      _Pragma("unroll") for (int u = 0; u < NU; ++u) if (pred[u]) {
         const uint4 res = nvls_scale<MODE>(v[u], a.scale);
         multimem_st_v4(mc + (s0 + idx[u]) * 16, res);
         if (!inplace) store_user<MODE>(buf, s0 + idx[u], count, fast, res);

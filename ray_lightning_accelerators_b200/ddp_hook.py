@@ -11,6 +11,9 @@ Reference call sites replaced:
 
 No NCCL on any of the three; the torch process group stays for control collectives (C9).
 """
+import contextlib
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -47,7 +50,7 @@ def allreduce_hook(state, bucket):
     buf = bucket.buffer()
     comm = state.comm
     wire = state.wire_dtype if (state.wire_dtype is not None and buf.dtype == torch.float32) else None
-    if state.register_buckets:
+    if state.register_buckets and not comm.in_nvls_arena(buf):
         comm.register(buf)  # no-op after the first step (cached by pointer)
     state.stream.wait_stream(torch.cuda.current_stream(buf.device))
     with torch.cuda.stream(state.stream):
@@ -135,6 +138,15 @@ class BufferSync:
             self.comm.broadcast(self.flat, root=self.root)
 
 
+def _want_nvls(comm):
+    """In-switch reduction pays off from ~4 ranks up (wire bytes (1 + 1/W) S against 2 (W-1)/W S for
+    peer-to-peer); B2C_NVLS=0/1 overrides."""
+    env = os.environ.get("B2C_NVLS")
+    if env is not None:
+        return env == "1"
+    return comm.world >= 4
+
+
 def wrap_ddp(model, comm, device_ids=None, wire_dtype=None, find_unused_parameters=True,
              bucket_cap_mb=25, gradient_as_bucket_view=False, process_group=None):
     """Build the DDP wrapper the way the reference's workers do (PTL 1.1.7 configure_ddp:
@@ -143,9 +155,18 @@ def wrap_ddp(model, comm, device_ids=None, wire_dtype=None, find_unused_paramete
     from torch.nn.parallel import DistributedDataParallel as DDP
     broadcast_module_states(comm, model, root=0)                 # C2 (instead of init_sync)
     bufsync = BufferSync(comm, model, root=0)                    # C4 set-up (re-points buffers)
-    ddp = DDP(model, device_ids=device_ids, find_unused_parameters=find_unused_parameters,
-              bucket_cap_mb=bucket_cap_mb, gradient_as_bucket_view=gradient_as_bucket_view,
-              broadcast_buffers=False, init_sync=False, process_group=process_group)
+    pool_ctx = contextlib.nullcontext()
+    if wire_dtype is None and comm.world > 1 and _want_nvls(comm):
+        # NVLink multicast arena sized for the gradients (x2 for allocator rounding); when it comes up
+        # DDP's buckets are allocated INSIDE it and every bucket allreduce runs in the switch, in place
+        grad_bytes = sum(p.numel() * p.element_size() for p in model.parameters() if p.requires_grad)
+        arena = int(os.environ.get("B2C_NVLS_ARENA_BYTES", 2 * grad_bytes + (64 << 20)))
+        if comm.enable_nvls(arena):
+            pool_ctx = torch.cuda.use_mem_pool(comm.torch_pool())
+    with pool_ctx:
+        ddp = DDP(model, device_ids=device_ids, find_unused_parameters=find_unused_parameters,
+                  bucket_cap_mb=bucket_cap_mb, gradient_as_bucket_view=gradient_as_bucket_view,
+                  broadcast_buffers=False, init_sync=False, process_group=process_group)
     state = B2cHookState(comm, wire_dtype=wire_dtype)
     ddp.register_comm_hook(state, allreduce_hook)                # C3
     if bufsync.flat is not None:

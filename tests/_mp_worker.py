@@ -166,7 +166,9 @@ def main():
         comm.check_alive()
         for t, want in outs2:
             assert torch.allclose(t, torch.full_like(t, want), rtol=1e-6, atol=0), "nvls stress"
-    comm.set_param(_lib.PARAM_NVLS_MIN_BYTES, 0)  # the DDP parity section below pins the rank-order contract
+    if world == 2:
+        comm.set_param(_lib.PARAM_NVLS_MIN_BYTES, 0)  # W=2 below pins bit-identity with NCCL (rank-order contract)
+    os.environ['B2C_NVLS'] = '1' if world > 2 else '0'  # W>2: DDP buckets live in the multicast arena
     # ---- DDP: our hook vs stock NCCL DDP, MLP (config #2) 100 steps, loss within 1e-5 relative
     def train(use_b2c):
         model = workloads.build_model("mnist_mlp", seed=0).to(dev)
@@ -226,7 +228,7 @@ def main():
     comm.close()
     dist.destroy_process_group()
     if rank == 0:
-        print(f"MP_WORKER_OK world={world} hidden={hidden} launches={st['launches']}")
+        print(f"MP_WORKER_OK world={world} hidden={hidden} launches={st['launches']} nvls={st['nvls_launches']} zc={st['zerocopy_launches']}")
 
 
 if __name__ == "__main__":
