@@ -142,7 +142,10 @@ def _build_worker(args, rank, world, local):
     model = workloads.build_model(args.model, seed=0)
     acc.model_to_device(model)
     opt = model.configure_optimizers()
-    ddp = _wrap(acc, model, args)
+    if args.impl == "nccl":   # on-box comparator: what RayAccelerator(use_gpu=True) resolves to upstream (ray_ddp.py:227)
+        ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=acc.get_device_ids(), find_unused_parameters=True)
+    else:
+        ddp = _wrap(acc, model, args)
     return acc, model, ddp, opt
 
 
@@ -184,7 +187,8 @@ def run_b2c(args):
                          "Use --impl reference for the reference's CPU path.")
     torch.backends.cudnn.benchmark = True
     acc, model, ddp, opt = _build_worker(args, rank, world, local)
-    comm, state = acc.b2c_comm, ddp._b2c_state
+    stock = args.impl == "nccl"
+    comm, state = acc.b2c_comm, (None if stock else ddp._b2c_state)
     dev = torch.device("cuda", torch.cuda.current_device())
     batch = args.batch
     K, W = args.steps, max(3, args.warmup)
@@ -206,7 +210,8 @@ def run_b2c(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    state.enable_timing()
+    if not stock:
+        state.enable_timing()
     st0 = comm.stats()
     launches0 = st0["launches"]
     torch.cuda.synchronize()
@@ -230,8 +235,9 @@ def run_b2c(args):
         grad_kernel, grad_path = f"k_allreduce_twoshot<f32,W={world}>", "libb2c.so: staged two-shot / one-shot through the arena"
     else:
         grad_kernel, grad_path = "k_allreduce_oneshot<f32,W=1>", "libb2c.so: W=1 scale pass (no peer)"
-    per_bucket_us, n_timed = _bucket_stats(state)
-    state.timing = None
+    per_bucket_us, n_timed = _bucket_stats(state) if not stock else ({}, 0)
+    if not stock:
+        state.timing = None
     ms_total = float(ms.item())
     value = world * batch * K / (ms_total / 1e3)
 
@@ -288,11 +294,12 @@ def run_b2c(args):
                 "busbw_GBps": (2.0 * (world - 1) / world * nb / per_bucket_us[nb] / 1e3) if world > 1 else None}
                for nb in sorted(per_bucket_us)]
 
-    allreduce = _allreduce_section(args, comm, rank, world, dev)
+    allreduce = _allreduce_section(args, comm, rank, world, dev) if not stock else None
     cpu_baseline = _cpu_baseline(args) if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
 
     if rank == 0:
         line = {
+            "impl": "b2c" if not stock else "nccl (stock torch DDP, on-box comparator; not the reference arm)",
             "metric": "train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32" if args.wire != "bf16" else "f32 grads on a bf16 wire",
@@ -399,7 +406,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="b2c", choices=["b2c", "reference"])
+    ap.add_argument("--impl", default="b2c", choices=["b2c", "reference", "nccl"])
     ap.add_argument("--model", default="resnet50")
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--wire", default="f32", choices=["f32", "bf16"])
