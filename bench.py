@@ -186,6 +186,8 @@ def run_b2c(args):
         raise SystemExit("bench.py (b2c arm) needs a CUDA device; there is no CPU fallback. "
                          "Use --impl reference for the reference's CPU path.")
     torch.backends.cudnn.benchmark = True
+    # room in the multicast arena for the allreduce section's buffers as well (bump allocator, never freed)
+    os.environ.setdefault("B2C_NVLS_ARENA_BYTES", str(2 << 30))
     acc, model, ddp, opt = _build_worker(args, rank, world, local)
     stock = args.impl == "nccl"
     comm, state = acc.b2c_comm, (None if stock else ddp._b2c_state)
@@ -356,6 +358,29 @@ def _allreduce_section(args, comm, rank, world, dev):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.sort().values[len(ts) // 2])
 
+    def pipelined(make, fn, S):
+        """Back-to-back launches over distinct buffers whose total footprint exceeds L2 (no flush
+        needed): launch latency and barrier skew overlap with the previous kernel, as they do for the
+        buckets of a real backward pass.  One event pair around 3 rounds; per-allreduce time."""
+        k = max(2, (192 << 20) // S + 1)
+        bufs = [make() for _ in range(k)]
+        for b in bufs:
+            fn(b)
+        torch.cuda.synchronize()
+        if world > 1:
+            comm.barrier()
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(3):
+            for b in bufs:
+                fn(b)
+        b_.record()
+        b_.synchronize()
+        t = torch.tensor([a.elapsed_time(b_) * 1e3 / (3 * k)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     if world > 1:
         for S in RESNET50_BUCKETS:
             if comm.nvls_enabled:
@@ -373,9 +398,30 @@ def _allreduce_section(args, comm, rank, world, dev):
             y = torch.randn(S // 4, device=dev)
             us_nccl = timed(lambda: dist.all_reduce(y), comm.barrier)
             bus = 2.0 * (world - 1) / world * S
-            out.append({"bytes": S, "path": path, "us": us, "busbw_GBps": bus / us / 1e3, "frac_of_900": bus / us / 1e3 / NVLINK_NOMINAL_GBPS,
-                        "nccl_us": us_nccl, "nccl_busbw_GBps": bus / us_nccl / 1e3})
-        return {"mode": f"nvlink W={world}", "timing": "median of %d, L2 flushed, max over ranks" % iters, "buckets": out}
+            row = {"bytes": S, "path": path, "us": us, "busbw_GBps": bus / us / 1e3, "frac_of_900": bus / us / 1e3 / NVLINK_NOMINAL_GBPS,
+                   "nccl_us": us_nccl, "nccl_busbw_GBps": bus / us_nccl / 1e3}
+            if S >= (8 << 20):
+                def make():
+                    if comm.nvls_enabled:
+                        try:
+                            t_ = comm.nvls_empty(S // 4)
+                            t_.normal_()
+                            return t_
+                        except MemoryError:
+                            pass
+                    t_ = torch.randn(S // 4, device=dev)
+                    comm.register(t_)
+                    return t_
+                up = pipelined(make, lambda t_: comm.allreduce(t_, algo=ALGO_AUTO), S)
+                un = pipelined(lambda: torch.randn(S // 4, device=dev), lambda t_: dist.all_reduce(t_), S)
+                row.update({"us_pipelined": up, "busbw_pipelined_GBps": bus / up / 1e3,
+                            "frac_of_900_pipelined": bus / up / 1e3 / NVLINK_NOMINAL_GBPS,
+                            "nccl_us_pipelined": un, "nccl_busbw_pipelined_GBps": bus / un / 1e3})
+            out.append(row)
+        return {"mode": f"nvlink W={world}",
+                "timing": "us: median of %d isolated launches, L2 flushed, ranks aligned, max over ranks; "
+                          "us_pipelined: back-to-back launches over distinct buffers > L2, max over ranks" % iters,
+                "buckets": out}
     g = LocalGroup(8, device=dev.index or 0, arena_bytes=8 << 20)
     g.set_param(_lib.PARAM_TIMEOUT_MS, 3000)
     for S in RESNET50_BUCKETS:

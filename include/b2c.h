@@ -239,6 +239,10 @@ int b2c_get_stats(b2c_comm* comm, b2c_stats* out);
 /* base address / size of one arena slot (device pointer, local rank) */
 int b2c_comm_arena(b2c_comm* comm, void** base, size_t* slot_bytes);
 int b2c_comm_info(b2c_comm* comm, int* rank, int* world, int* device);
+/* Device-side phase clock of the LAST kernel of this comm (channel 0, %globaltimer ns):
+ * out[0] kernel start, out[1] passed barrier A, out[2] passed barrier B, out[3] end.
+ * Synchronises the device; a profiling aid, not for the hot path. */
+int b2c_get_phase_ns(b2c_comm* comm, uint64_t out[4]);
 
 #ifdef __cplusplus
 }

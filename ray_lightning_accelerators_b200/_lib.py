@@ -113,6 +113,7 @@ SIGNATURES = {
     "b2c_get_param": (_int, [_vp, _int, _c.POINTER(_c.c_long)]),
     "b2c_get_stats": (_int, [_vp, _c.POINTER(Stats)]),
     "b2c_comm_arena": (_int, [_vp, _pp, _c.POINTER(_sz)]),
+    "b2c_get_phase_ns": (_int, [_vp, _c.POINTER(_c.c_uint64 * 4)]),
     "b2c_comm_info": (_int, [_vp, _c.POINTER(_int), _c.POINTER(_int), _c.POINTER(_int)]),
 }
 

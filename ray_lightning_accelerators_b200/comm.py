@@ -78,6 +78,15 @@ class _Base:
         _lib.check(self._lib.b2c_get_stats(self._first, ctypes.byref(s)))
         return s.as_dict()
 
+    def phase_us(self):
+        """(to barrier A, A to B, B to end) of the last kernel's channel 0, in microseconds (syncs)."""
+        out = (ctypes.c_uint64 * 4)()
+        _lib.check(self._lib.b2c_get_phase_ns(self._first, ctypes.byref(out)))
+        t = list(out)
+        if t[2] < t[1]:  # kernels with a single barrier (one-shot, broadcast) leave slot 2 stale
+            t[2] = t[3]
+        return ((t[1] - t[0]) / 1e3, (t[2] - t[1]) / 1e3, (t[3] - t[2]) / 1e3)
+
     def check_alive(self):
         """Raise if a kernel reported a flag-barrier timeout (sticky)."""
         st = self.stats()

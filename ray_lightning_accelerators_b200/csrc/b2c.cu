@@ -1256,6 +1256,13 @@ extern "C" int b2c_comm_arena(b2c_comm* c, void** base, size_t* slot_bytes) {
   if (slot_bytes) *slot_bytes = c->slot_bytes;
   return B2C_OK;
 }
+extern "C" int b2c_get_phase_ns(b2c_comm* c, uint64_t out[4]) {
+  if (!c || !out) return fail(B2C_EINVAL, "b2c_get_phase_ns: NULL argument");
+  DeviceGuard g(c->device);
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy(out, c->region + B2C_CTL_PHASE_U64 * 8, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  return B2C_OK;
+}
 extern "C" int b2c_comm_info(b2c_comm* c, int* rank, int* world, int* device) {
   if (!c) return fail(B2C_EINVAL, "b2c_comm_info: comm is NULL");
   if (rank) *rank = c->rank;

@@ -29,6 +29,7 @@
 #define B2C_CTL_EPOCH 0
 #define B2C_CTL_CALLS 1
 #define B2C_CTL_TICKET 2
+#define B2C_CTL_PHASE_U64 8   /* u64 index: start, after barrier A, after barrier B, end (channel 0) */
 
 static_assert(B2C_MAX_BLOCKS * B2C_MAX_WORLD * 4 <= B2C_FLAG_BYTES && B2C_CTL_BYTES + B2C_FLAG_BYTES <= B2C_HEADER_BYTES, "flag page too small");
 
@@ -258,12 +259,16 @@ __device__ __forceinline__ Ctx prologue(const B2cKArgs& a) {
   c.calls = ld_volatile_u32(c.ctl + B2C_CTL_CALLS);
   c.slot_off = (size_t)B2C_HEADER_BYTES + (size_t)(c.calls & 1u) * a.slot_bytes;
   c.dead = false;
+  if (blockIdx.x == 0 && threadIdx.x == 0)  // phase clock of channel 0 (read back by b2c_get_phase_ns)
+    reinterpret_cast<unsigned long long*>(c.ctl)[B2C_CTL_PHASE_U64] = globaltimer_ns();
   return c;
 }
 
 // last CTA out advances the epoch / call counters for the next launch on this stream
 __device__ __forceinline__ void epilogue(const Ctx& c) {
   __syncthreads();
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    reinterpret_cast<unsigned long long*>(c.ctl)[B2C_CTL_PHASE_U64 + 3] = globaltimer_ns();
   if (threadIdx.x == 0) {
     __threadfence();
     unsigned t = atomicAdd(c.ctl + B2C_CTL_TICKET, 1u);
@@ -309,6 +314,8 @@ __device__ __forceinline__ void channel_barrier(const B2cKArgs& a, Ctx& c, uint3
   }
   __syncthreads();
   if (*s_dead) c.dead = true;
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    reinterpret_cast<unsigned long long*>(c.ctl)[B2C_CTL_PHASE_U64 + ((target - c.epoch) & 3u)] = globaltimer_ns();
 }
 
 // iterate vectors i of [0, n) owned by channel c.b, U at a time per thread.
