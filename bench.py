@@ -212,7 +212,7 @@ def run_b2c(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    if not stock:
+    if not stock and not args.no_bucket_timing:
         state.enable_timing()
     st0 = comm.stats()
     launches0 = st0["launches"]
@@ -237,7 +237,7 @@ def run_b2c(args):
         grad_kernel, grad_path = f"k_allreduce_twoshot<f32,W={world}>", "libb2c.so: staged two-shot / one-shot through the arena"
     else:
         grad_kernel, grad_path = "k_allreduce_oneshot<f32,W=1>", "libb2c.so: W=1 scale pass (no peer)"
-    per_bucket_us, n_timed = _bucket_stats(state) if not stock else ({}, 0)
+    per_bucket_us, n_timed = _bucket_stats(state) if (not stock and state.timing is not None) else ({}, 0)
     if not stock:
         state.timing = None
     ms_total = float(ms.item())
@@ -478,6 +478,7 @@ def main():
     ap.add_argument("--ref-batch", type=int, default=16)
     ap.add_argument("--ref-max-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-bucket-timing", action="store_true", help="no per-bucket CUDA events in the hook (host-bound tiny models)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
