@@ -143,7 +143,7 @@ static void default_params(b2c_comm* c) {
   c->params[B2C_PARAM_MAX_BLOCKS_BCAST] = 32;
   c->params[B2C_PARAM_ZEROCOPY] = 1;
   c->params[B2C_PARAM_ZEROCOPY_MIN_BYTES] = 256 * 1024;
-  c->params[B2C_PARAM_NVLS_MIN_BYTES] = 64 * 1024;
+  c->params[B2C_PARAM_NVLS_MIN_BYTES] = 512 * 1024;  // below this one barrier (staged one-shot) beats two
   c->params[B2C_PARAM_MAX_BLOCKS_NVLS] = 8;   // the switch saturates with 4-8 CTAs; more only adds congestion
   c->params[B2C_PARAM_UNROLL_NVLS] = 8;
   c->params[B2C_PARAM_UNROLL_ZC] = 0;
