@@ -236,7 +236,7 @@ def run_b2c(args):
     elif world > 1:
         grad_kernel, grad_path = f"k_allreduce_twoshot<f32,W={world}>", "libb2c.so: staged two-shot / one-shot through the arena"
     else:
-        grad_kernel, grad_path = "k_allreduce_oneshot<f32,W=1>", "libb2c.so: W=1 scale pass (no peer)"
+        grad_kernel, grad_path = "k_scale_inplace<f32>", "libb2c.so: W=1 in-place scale pass (no peer)"
     per_bucket_us, n_timed = _bucket_stats(state) if (not stock and state.timing is not None) else ({}, 0)
     if not stock:
         state.timing = None
@@ -298,7 +298,7 @@ def run_b2c(args):
         us = per_bucket_us[dom]
         if world == 1:
             alg = 2.0 * dom  # read S, write S (W = 1: scale pass in place)
-            roofline = {"bound": "hbm", "kernel": "k_allreduce_oneshot<f32,W=1>", "achieved": alg / us / 1e3,
+            roofline = {"bound": "hbm", "kernel": grad_kernel, "achieved": alg / us / 1e3,
                         "peak": peaks["hbm_gbs"], "peak_kind": f"{peak_kind} HBM copy", "unit": "GB/s",
                         "frac": alg / us / 1e3 / peaks["hbm_gbs"], "traffic": None,
                         "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom}

@@ -593,6 +593,25 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
     }
   }
 
+  // ---- a single rank: streaming scale pass, no arena, no flags
+  if (W == 1 && mode != MODE_F32_BF16 && (((uintptr_t)bufs[c->rank < 0 ? 0 : c->rank]) & 15u) == 0) {
+    void* b = bufs[c->rank];
+    const size_t nvec = count / vw;
+    size_t blocks = (nvec + 256 * 4 - 1) / (256 * 4);
+    if (blocks < 1) blocks = 1;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (mode == MODE_F32) k_scale_inplace<MODE_F32><<<(unsigned)blocks, 256, 0, stream>>>(b, count, scale);
+    else k_scale_inplace<MODE_BF16><<<(unsigned)blocks, 256, 0, stream>>>(b, count, scale);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch (scale pass)");
+    c->stats.launches++;
+    c->stats.oneshot_launches++;
+    c->stats.last_algo = B2C_ALGO_ONESHOT;
+    c->stats.last_blocks = (uint32_t)blocks;
+    c->stats.last_threads = 256;
+    return B2C_OK;
+  }
+
   const size_t slot_vecs = c->slot_bytes / 16;
   // pieces keep 16-byte alignment relative to buf; a single rank never touches the arena, so no split
   const size_t piece_elems = (W == 1) ? (count > 0 ? count : 1) : slot_vecs * vw;

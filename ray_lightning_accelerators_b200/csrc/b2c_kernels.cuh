@@ -681,3 +681,32 @@ __global__ void __launch_bounds__(512, 1) k_allreduce_nvls(const __grid_constant
   }
   epilogue(c);
 }
+
+
+// ================================================================= W = 1: in-place scale pass
+// A single rank has nothing to exchange: out = in * scale (one rounding).  Plain HBM-bound
+// streaming kernel — no flags, no counters, small register footprint so that many CTAs share an SM
+// next to the backward kernels.  16-byte aligned buffers only (the generic one-shot kernel takes
+// the rest); the ragged tail (< one vector) is handled by the last thread block's first warp.
+template <int MODE>
+__global__ void __launch_bounds__(256) k_scale_inplace(void* __restrict__ buf, size_t count, float scale) {
+  constexpr int VW = Mode<MODE>::VW;
+  const size_t nfull = count / VW;
+  uint4* p = static_cast<uint4*>(buf);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < nfull; i += 4 * stride) {
+    uint4 v0 = p[i], v1 = p[i + stride], v2 = p[i + 2 * stride], v3 = p[i + 3 * stride];
+    Acc<MODE> a0, a1, a2, a3;
+    a0.init(v0, scale); a1.init(v1, scale); a2.init(v2, scale); a3.init(v3, scale);
+    p[i] = a0.finish(); p[i + stride] = a1.finish(); p[i + 2 * stride] = a2.finish(); p[i + 3 * stride] = a3.finish();
+  }
+  for (; i < nfull; i += stride) {
+    Acc<MODE> a; a.init(p[i], scale);
+    p[i] = a.finish();
+  }
+  if (blockIdx.x == gridDim.x - 1) {
+    const size_t e = nfull * VW + threadIdx.x;
+    if (e < count) Elem<MODE>::st(buf, e, __fmul_rn(Elem<MODE>::ld(buf, e), scale));
+  }
+}
