@@ -149,10 +149,6 @@ def _build_worker(args, rank, world, local):
     return acc, model, ddp, opt
 
 
-class _Plain(object):
-    pass
-
-
 def _wrap(acc, model, args):
     """configure_ddp, but wrapping the bare module: the bench calls forward(x) directly."""
     import torch

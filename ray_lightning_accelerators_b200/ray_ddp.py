@@ -23,7 +23,7 @@ import torch
 from . import _ray as ray
 from .mini_pl import StepModule
 from .session import init_session
-from .tune import TUNE_INSTALLED, is_session_enabled
+from .tune import is_session_enabled
 from .util import Queue, pin_gpu, process_results
 
 
