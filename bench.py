@@ -306,6 +306,16 @@ def run_b2c(args):
                         "frac": alg / us / 1e3 / NVLINK_NOMINAL_GBPS,
                         "frac_of_measured_copy": alg / us / 1e3 / NVLINK_MEASURED_COPY_GBPS, "traffic": None,
                         "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom}
+    if roofline is not None:
+        try:  # per-launch DRAM bytes of this kernel from the committed ncu --set full capture
+            with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as f:
+                cap = json.load(f).get(roofline["kernel"])
+            if cap:
+                roofline["traffic"] = cap["dram_bytes_read"] + cap["dram_bytes_write"]
+                roofline["traffic_note"] = (f"ncu --set full, isolated launch on a {cap['bucket_bytes']} B bucket "
+                                            "(results still L2-resident at kernel end, so DRAM writes are not counted)")
+        except Exception:
+            pass
     buckets = [{"bytes": nb, "us": per_bucket_us[nb],
                 "busbw_GBps": (2.0 * (world - 1) / world * nb / per_bucket_us[nb] / 1e3) if world > 1 else None}
                for nb in sorted(per_bucket_us)]
