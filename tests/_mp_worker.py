@@ -169,6 +169,8 @@ def main():
     if world == 2:
         comm.set_param(_lib.PARAM_NVLS_MIN_BYTES, 0)  # W=2 below pins bit-identity with NCCL (rank-order contract)
     os.environ['B2C_NVLS'] = '1' if world > 2 else '0'  # W>2: DDP buckets live in the multicast arena
+    if world > 2:
+        comm.set_param(_lib.PARAM_NVLS_MIN_BYTES, 1024)  # the MLP's 111 KB bucket goes through the switch too
     # ---- DDP: our hook vs stock NCCL DDP, MLP (config #2) 100 steps, loss within 1e-5 relative
     def train(use_b2c):
         model = workloads.build_model("mnist_mlp", seed=0).to(dev)
