@@ -182,6 +182,14 @@ class DistributedOptimizer:
         self._handles = []
         self._stream = torch.cuda.Stream(priority=-1) if _st["comm"] is not None else None
         cap = bucket_bytes or _BUCKET_BYTES
+        comm = _st["comm"]
+        if comm is not None and params:
+            from .ddp_hook import _want_nvls
+            if _want_nvls(comm):
+                # from ~4 ranks up the gradient buckets live in the NVLink-multicast arena and are
+                # reduced in the switch, in place (collective set-up, once)
+                total = sum(p.numel() * p.element_size() for p in params)
+                comm.enable_nvls(int(os.environ.get("B2C_NVLS_ARENA_BYTES", 2 * total + (64 << 20))))
         run, nbytes, key = [], 0, None
         for p in reversed(params):
             k = (p.dtype, p.device)
@@ -206,13 +214,21 @@ class DistributedOptimizer:
         for p in run:
             offs.append(total)
             total += (p.numel() * es + 15) // 16 * 16 // es
-        flat = torch.zeros(total, dtype=run[0].dtype, device=run[0].device)
+        comm = _st["comm"]
+        flat = None
+        if comm is not None and run[0].is_cuda and comm.nvls_enabled:
+            try:
+                flat = comm.nvls_empty(total, run[0].dtype).zero_()
+            except MemoryError:
+                flat = None
+        if flat is None:
+            flat = torch.zeros(total, dtype=run[0].dtype, device=run[0].device)
         for p, off in zip(run, offs):
             p.grad = flat[off:off + p.numel()].view_as(p)
             p._b2c_grad_view = p.grad
             self._bucket_of[p] = len(self._buckets)
-        if _st["comm"] is not None and flat.is_cuda:
-            _st["comm"].register(flat)  # zero-copy from the first step on (collective)
+        if comm is not None and flat.is_cuda and not comm.in_nvls_arena(flat):
+            comm.register(flat)  # zero-copy from the first step on (collective)
         self._buckets.append((flat, list(run)))
 
     def _on_grad(self, p):

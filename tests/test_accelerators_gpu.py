@@ -58,6 +58,23 @@ def test_horovod_accelerator_two_gpus(tmp_path):
     train_test(trainer, BoringModel())
 
 
+def test_horovod_accelerator_four_gpus_buckets_in_multicast_arena(tmp_path):
+    """From 4 slots up the shim's gradient buckets are allocated inside the NVLink-multicast arena."""
+    _need(4)
+
+    class Check(Callback):
+        def on_epoch_end(self, trainer, pl_module):
+            from ray_lightning_accelerators_b200 import hvd_shim
+            comm = hvd_shim._st["comm"]
+            assert comm.nvls_enabled, comm.nvls_error
+            assert all(comm.in_nvls_arena(p.grad) for p in pl_module.parameters())
+            comm.check_alive()
+
+    trainer = get_trainer(tmp_path, HorovodRayAccelerator(num_hosts=1, num_slots=4, use_gpu=True), use_gpu=True,
+                          callbacks=[Check()])
+    train_test(trainer, BoringModel())
+
+
 def test_gpu_runs_match_cpu_gloo_reference(tmp_path):
     """Same seed, same data: the weights the driver gets back from the 2-GPU b2c run equal the ones
     from the reference's CPU configuration (gloo) to fp32 round-off (Linear(32,2), 10 SGD steps)."""
