@@ -349,6 +349,96 @@ def run_b2c(args):
     dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------- Horovod-style arm
+def run_hvd(args):
+    """BASELINE configs[3]: the HorovodRayAccelerator worker path (ray_horovod.py:146-169) on the hvd shim —
+    hvd.init, LR x size, broadcast_parameters / optimizer state, DistributedOptimizer, backward +
+    synchronize() + step — with the model held in --param-dtype (bf16 for BERT: bf16 gradients, fp32
+    accumulate in the kernel, one rounding).  --hvd-backend nccl runs the same loop with a per-bucket NCCL
+    all_reduce instead of libb2c.so, as the on-box comparator."""
+    import torch
+    import torch.distributed as dist
+    from examples import workloads
+    from ray_lightning_accelerators_b200 import HorovodRayAccelerator, hvd_shim as hvd
+    from ray_lightning_accelerators_b200.mini_pl import Trainer
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    use_gpu = torch.cuda.is_available()
+    if not use_gpu and not args.allow_cpu:
+        raise SystemExit("bench.py --impl hvd needs a CUDA device (or --allow-cpu for the gloo plumbing check)")
+    addr = os.environ.get("MASTER_ADDR", "127.0.0.1")
+    port = os.environ.get("MASTER_PORT") or str(_free_port())
+    hvd.init(rank=rank, size=world, local_rank=local, address=f"tcp://{addr}:{port}", use_gpu=use_gpu)
+    stock = args.hvd_backend == "nccl"
+    comm = hvd._st["comm"]
+    if stock and comm is not None:   # comparator: drop the b2c communicator, the shim then uses the process group
+        hvd._st["comm"] = None
+    acc = HorovodRayAccelerator(num_hosts=1, num_slots=world, use_gpu=use_gpu)
+    acc.trainer = Trainer(gpus=int(use_gpu), accelerator=acc, checkpoint_callback=False)
+    model = workloads.build_model(args.model, seed=0)
+    if args.param_dtype == "bf16":
+        model = model.to(torch.bfloat16)
+    optimizers, _, dev = acc._horovod_setup(model)
+    opt = optimizers[0]
+    batch, K, W = args.batch, args.steps, max(3, args.warmup)
+    x, y = [t.to(dev) if t is not None else None for t in workloads.synthetic_batch(args.model, batch, rank, 0)]
+
+    def step():
+        opt.zero_grad()
+        loss = model.loss_fn(model(x), y)
+        loss.backward()
+        opt.synchronize()
+        with opt.skip_synchronize():
+            opt.step()
+        return loss
+
+    def sync():
+        if use_gpu:
+            torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(W):
+        step()
+    sync()
+    st0 = comm.stats() if (comm is not None and not stock) else None
+    if use_gpu:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        loss = step()
+    if use_gpu:
+        e1.record()
+    sync()
+    ms = e0.elapsed_time(e1) if use_gpu else (time.perf_counter() - t0) * 1e3
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    st1 = comm.stats() if st0 is not None else None
+    grad_bytes = sum(f.numel() * f.element_size() for f, _ in opt._buckets)
+    if rank == 0:
+        line = {"impl": "b2c-hvd" if not stock else "hvd loop on NCCL all_reduce (on-box comparator)",
+                "metric": "train_samples_per_sec", "value": world * batch * K / (ms / 1e3), "unit": "samples/s",
+                "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": args.param_dtype, "data": "synthetic",
+                "config": {"workload": f"{args.model} seq 128 batch {batch}/GPU via HorovodRayAccelerator worker path "
+                                       f"(BASELINE configs[3])", "global_batch": batch * world, "parallelism": f"dp{world}",
+                           "grad_buckets": [f.numel() * f.element_size() for f, _ in opt._buckets],
+                           "grad_bytes_per_step": grad_bytes},
+                "last_loss": float(loss.item()),
+                "gpu_launches": int(st1["launches"] - st0["launches"]) if st1 else 0,
+                "paths": {k: int(st1[k] - st0[k]) for k in ("nvls_launches", "zerocopy_launches", "oneshot_launches",
+                                                            "twoshot_launches")} if st1 else None}
+        print(json.dumps(line), flush=True)
+    if stock and comm is not None:
+        hvd._st["comm"] = comm
+    hvd.shutdown()
+
+
 RESNET50_BUCKETS = [12415000, 31500000, 29664000, 27021000, 1625000]  # bytes, launch order (BASELINE.md §3)
 
 
@@ -476,7 +566,10 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="b2c", choices=["b2c", "reference", "nccl"])
+    ap.add_argument("--impl", default="b2c", choices=["b2c", "reference", "nccl", "hvd"])
+    ap.add_argument("--param-dtype", default="f32", choices=["f32", "bf16"])
+    ap.add_argument("--hvd-backend", default="b2c", choices=["b2c", "nccl"])
+    ap.add_argument("--allow-cpu", action="store_true")
     ap.add_argument("--model", default="resnet50")
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--wire", default="f32", choices=["f32", "bf16"])
@@ -488,6 +581,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.impl == "hvd":
+        run_hvd(args)
     else:
         run_b2c(args)
 

@@ -68,6 +68,26 @@ class _Classifier(nn.Module):
         return torch.optim.SGD(self.parameters(), lr=self.lr, momentum=self.momentum)
 
 
+class _BertMLM(nn.Module):
+    """BERT masked-LM (BASELINE configs[3]: BERT-base bf16 behind HorovodRayAccelerator): forward
+    returns the logits, the loss is token cross-entropy in fp32."""
+
+    def __init__(self, layers=12, lr=1e-4):
+        super().__init__()
+        from transformers import BertConfig, BertForMaskedLM
+        self.net = BertForMaskedLM(BertConfig(num_hidden_layers=layers))
+        self.lr = lr
+
+    def forward(self, x):
+        return self.net(input_ids=x).logits
+
+    def loss_fn(self, out, y):
+        return F.cross_entropy(out.float().view(-1, out.size(-1)), y.view(-1))
+
+    def configure_optimizers(self):
+        return torch.optim.AdamW(self.parameters(), lr=self.lr)
+
+
 def build_model(name, seed=0):
     """Random-init weights of the named architecture, seeded like PL_GLOBAL_SEED
     (ray_ddp.py:154-159 forwards it to every worker)."""
@@ -82,6 +102,10 @@ def build_model(name, seed=0):
     if name == "resnet18":
         import torchvision
         return _Classifier(torchvision.models.resnet18())
+    if name == "bert_base":
+        return _BertMLM(layers=12)
+    if name == "bert_tiny":
+        return _BertMLM(layers=1)
     raise ValueError(f"unknown workload {name}")
 
 
@@ -95,7 +119,10 @@ def synthetic_batch(name, batch, rank, step=0, seed=1000):
         return torch.randn(batch, 32, generator=g), None
     if name in ("resnet50", "resnet18"):
         return torch.randn(batch, 3, 224, 224, generator=g), torch.randint(0, 1000, (batch,), generator=g)
+    if name in ("bert_base", "bert_tiny"):
+        ids = torch.randint(0, 30522, (batch, 128), generator=g)
+        return ids, ids.clone()
     raise ValueError(name)
 
 
-DEFAULT_BATCH = {"mnist_mlp": 32, "boring": 1, "resnet50": 256, "resnet18": 64}
+DEFAULT_BATCH = {"mnist_mlp": 32, "boring": 1, "resnet50": 256, "resnet18": 64, "bert_base": 32, "bert_tiny": 4}
