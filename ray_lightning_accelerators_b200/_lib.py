@@ -167,3 +167,40 @@ def last_error():
 def check(rc):
     if rc != 0:
         raise B2cError(rc, last_error())
+
+
+# ---------------------------------------------------------------- optional C++ DDP hook (torch extension)
+HOOK_SRC = os.path.join(CSRC_DIR, "b2c_torch_hook.cpp")
+HOOK_PATH = os.path.join(_HERE, "_b2c_torch_hook.so")
+_hook_mod = None
+
+
+def build_torch_hook(verbose=False):
+    """Compile csrc/b2c_torch_hook.cpp in-tree (needs torch headers; no GPU).  The only torch-aware
+    binary of the package; libb2c.so itself stays torch-free."""
+    import shutil
+    from torch.utils.cpp_extension import load
+    build_dir = os.path.join(_HERE, "_hook_build")
+    os.makedirs(build_dir, exist_ok=True)
+    os.environ.setdefault("TORCH_CUDA_ARCH_LIST", "10.0a")
+    mod = load(name="_b2c_torch_hook", sources=[HOOK_SRC], build_directory=build_dir, with_cuda=True,
+               extra_cflags=["-O2"], verbose=verbose)
+    shutil.copyfile(mod.__file__, HOOK_PATH)
+    return HOOK_PATH
+
+
+def load_torch_hook():
+    """The built extension module, or None when it has not been built (the Python hook is used then)."""
+    global _hook_mod
+    if _hook_mod is None and os.path.exists(HOOK_PATH):
+        import importlib.util
+        import torch  # noqa: F401  (its symbols must be loaded first)
+        spec = importlib.util.spec_from_file_location("_b2c_torch_hook", HOOK_PATH)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        _hook_mod = mod
+    return _hook_mod
+
+
+def fn_address(name):
+    return ctypes.cast(getattr(load(), name), ctypes.c_void_p).value

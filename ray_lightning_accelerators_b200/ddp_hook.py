@@ -210,7 +210,15 @@ def wrap_ddp(model, comm, device_ids=None, wire_dtype=None, find_unused_paramete
                   bucket_cap_mb=bucket_cap_mb, gradient_as_bucket_view=gradient_as_bucket_view,
                   broadcast_buffers=False, init_sync=False, process_group=process_group)
     state = B2cHookState(comm, wire_dtype=wire_dtype)
-    ddp.register_comm_hook(state, allreduce_hook)                # C3
+    cpp = _lib.load_torch_hook() if (os.environ.get("B2C_CPP_HOOK") == "1" and wire_dtype is None) else None
+    if cpp is not None:
+        # opt-in: the same hook logic as a c10d::CommHookInterface, no Python frame per bucket
+        state.cpp_hook_id = cpp.register_hook(ddp.reducer, _lib.fn_address("b2c_allreduce"),
+                                              _lib.fn_address("b2c_last_error"), comm._h.value, 1.0 / comm.world,
+                                              ALGO_AUTO, B2cHookState.INLINE_BYTES)
+        state.cpp_hook = cpp
+    else:
+        ddp.register_comm_hook(state, allreduce_hook)            # C3
     if bufsync.flat is not None:
         ddp.register_forward_pre_hook(bufsync)                   # C4 per step
     ddp._b2c_state = state
