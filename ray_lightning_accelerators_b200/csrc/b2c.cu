@@ -538,9 +538,14 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
     Nvls* nv = c->nvls;
     char* p = (char*)bufs[c->rank];
     const bool inside = nvls_inside;
-    const size_t piece = inside ? count : (nv->slot_bytes / 16) * vw;
-    for (size_t off = 0; off < count; off += piece) {
-      const size_t n = (count - off < piece) ? count - off : piece;
+    // In place the kernel works on whole 16-byte vectors of the caller's tensor.  A ragged tail (fewer
+    // than one vector) must not drag its neighbours in the arena into the reduction, so it goes through
+    // the staged one-shot kernel as a second, tiny launch.
+    const size_t tail = inside ? count % (size_t)vw : 0;
+    const size_t body = count - tail;
+    const size_t piece = inside ? (body ? body : 1) : (nv->slot_bytes / 16) * vw;
+    for (size_t off = 0; off < body; off += piece) {
+      const size_t n = (body - off < piece) ? body - off : piece;
       Launch L;
       fill_common(c, L.args, false);
       L.args.buf[c->rank] = p + off * ub;
@@ -558,6 +563,18 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
       c->stats.last_algo = B2C_ALGO_NVLS;
       rc = do_launch(c, L, 1, stream);
       if (rc) return rc;
+    }
+    if (tail) {
+      void* tb[B2C_MAX_WORLD] = {0};
+      tb[c->rank] = p + body * ub;
+      c->stats.calls_allreduce--;                       // one user call, two launches
+      c->stats.bytes_allreduce -= (uint64_t)tail * ub;
+      const long keep = c->params[B2C_PARAM_ZEROCOPY];
+      c->params[B2C_PARAM_ZEROCOPY] = 0;
+      rc = allreduce_impl(c, tb, false, tail, dtype, wire, scale, B2C_ALGO_ONESHOT, stream);
+      c->params[B2C_PARAM_ZEROCOPY] = keep;
+      if (rc) return rc;
+      c->stats.last_algo = B2C_ALGO_NVLS;
     }
     return B2C_OK;
   }

@@ -143,6 +143,17 @@ def main():
                     t0 = t.clone()
                     dist.broadcast(t0, src=0)
                     assert torch.equal(bits(t0), bits(t)), "nvls replicas differ"
+        # a ragged slice inside the arena: its neighbours must not be touched by the in-place kernel
+        big = comm.nvls_empty(4096)
+        big.fill_(7.0)
+        grads = [O.payload("int", 1003, r) for r in range(world)]
+        sl = big[:1003]
+        sl.copy_(torch.from_numpy(grads[rank]))
+        comm.allreduce(sl, algo=ALGO_NVLS)
+        torch.cuda.synchronize()
+        assert bool((big[1003:] == 7.0).all()), "NVLS in place wrote past the end of the tensor"
+        if world in (2, 4, 8):
+            assert np.array_equal(sl.cpu().numpy().view(np.uint32), O.b2c_allreduce_f32(grads).view(np.uint32))
         gb = [O.to_bf16_bits(O.payload("randn", 1 << 20, r)) for r in range(world)]
         t = torch.from_numpy(gb[rank].view(np.int16).copy()).to(dev).view(torch.bfloat16)
         comm.allreduce(t, algo=ALGO_NVLS)
