@@ -134,7 +134,9 @@ def main():
                     comm.allreduce(t, algo=ALGO_NVLS)
                     torch.cuda.synchronize()
                     comm.check_alive()
-                    assert comm.stats()["nvls_launches"] > z0
+                    st_ = comm.stats()
+                    assert st_["last_algo"] == ALGO_NVLS
+                    assert st_["nvls_launches"] > z0 or (inplace and n < 4)  # in place, < 1 vector: all tail
                     got = t.cpu().numpy()
                     if kind == "int" and world in (2, 4, 8):
                         assert torch.equal(bits(t), bits(ref)), ("nvls int bit-exact", n, inplace)
