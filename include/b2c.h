@@ -189,7 +189,8 @@ int b2c_deregister(b2c_comm* comm, void* ptr);
  *   b2c_nvls_bind    bind + map (unicast and multicast views); -- host barrier -- ready
  * b2c_nvls_arena returns the local unicast view: tensors placed inside it are reduced in
  * place (no staging) when passed to b2c_allreduce with algo NVLS/AUTO at the same offset on
- * every rank.  Arithmetic: the switch adds in fp32 in its own order and the result is scaled
+ * every rank (16-byte aligned; a ragged tail of less than one 16-byte vector is reduced by a
+ * second, staged launch so that bytes after the tensor are never touched).  Arithmetic: the switch adds in fp32 in its own order and the result is scaled
  * afterwards (sum * scale): within the stated tolerances of the reference path, bitwise
  * identical across replicas, but NOT bit-identical to the rank-order contract of the other
  * algorithms.  No reference counterpart (NCCL's NVLS algorithm is the upstream analogue). */
