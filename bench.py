@@ -159,12 +159,10 @@ def _wrap(acc, model, args):
 
 
 def _bucket_stats(state):
-    """Per-launch device times recorded by the hook around every b2c_allreduce of the timed region."""
-    import torch
-    torch.cuda.synchronize()
+    """Per-launch device times recorded by the hook (Python or C++) around every b2c_allreduce of the timed region."""
     by_size = {}
-    for e0, e1, nbytes in state.timing:
-        by_size.setdefault(nbytes, []).append(e0.elapsed_time(e1) * 1e3)
+    for us, nbytes in state.collect_timing_us():
+        by_size.setdefault(nbytes, []).append(us)
     return {nb: sum(v) / len(v) for nb, v in by_size.items()}, sum(len(v) for v in by_size.values())
 
 

@@ -18,6 +18,8 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <c10/cuda/CUDAStream.h>
 
+#include <deque>
+
 namespace {
 
 using allreduce_fn = int (*)(void* comm, void* buf, size_t count, int dtype, int wire_dtype, float scale, int algo,
@@ -34,6 +36,14 @@ struct HookState {
   bool side_used = false;
   int64_t buckets = 0;
   c10::optional<c10::cuda::CUDAStream> side;
+  // optional per-bucket device timing (bench.py's in-step roofline): event pairs around every call
+  struct Timed {
+    at::cuda::CUDAEvent start{cudaEventDefault};
+    at::cuda::CUDAEvent stop{cudaEventDefault};
+    int64_t nbytes = 0;
+  };
+  bool timing = false;
+  std::deque<Timed> timed;
 };
 
 class B2cCommHook : public c10d::CommHookInterface {
@@ -70,7 +80,7 @@ class B2cCommHook : public c10d::CommHookInterface {
         ev.record(*st_->side);
         ev.block(cur);
       }
-      call(buf, dtype, cur.stream());
+      timed_call(buf, dtype, cur, nbytes);
       auto fut = c10::make_intrusive<c10::ivalue::Future>(c10::TensorType::get(), devices);
       finish(fut, buf);
       return fut;
@@ -81,7 +91,7 @@ class B2cCommHook : public c10d::CommHookInterface {
     ready.record(cur);
     ready.block(*st_->side);
     c10::cuda::CUDAStreamGuard guard(*st_->side);  // the Future records its event on the current stream
-    call(buf, dtype, st_->side->stream());
+    timed_call(buf, dtype, *st_->side, nbytes);
     auto fut = c10::make_intrusive<c10::ivalue::Future>(c10::TensorType::get(), devices);
     finish(fut, buf);
     return fut;
@@ -101,6 +111,18 @@ class B2cCommHook : public c10d::CommHookInterface {
                                   stream);
     if (rc != 0 && error_.empty())
       error_ = "b2c_allreduce failed (" + std::to_string(rc) + "): " + (st_->last_error ? st_->last_error() : "?");
+  }
+  void timed_call(at::Tensor& buf, int dtype, const c10::cuda::CUDAStream& stream, size_t nbytes) {
+    if (!st_->timing) {
+      call(buf, dtype, stream.stream());
+      return;
+    }
+    st_->timed.emplace_back();
+    auto& t = st_->timed.back();
+    t.nbytes = (int64_t)nbytes;
+    t.start.record(stream);
+    call(buf, dtype, stream.stream());
+    t.stop.record(stream);
   }
   void finish(const c10::intrusive_ptr<c10::ivalue::Future>& fut, at::Tensor& buf) {
     if (error_.empty()) {
@@ -137,6 +159,25 @@ int64_t register_hook(const std::shared_ptr<c10d::Reducer>& reducer, uint64_t fn
   return (int64_t)registry().size() - 1;
 }
 
+void enable_timing(int64_t id, bool on) {
+  TORCH_CHECK(id >= 0 && (size_t)id < registry().size(), "bad hook id");
+  registry()[id]->timing = on;
+  if (!on) registry()[id]->timed.clear();
+}
+
+// (microseconds, bytes) of every call since timing was enabled; waits for the events, then forgets them
+std::vector<std::pair<double, int64_t>> collect_timing(int64_t id) {
+  TORCH_CHECK(id >= 0 && (size_t)id < registry().size(), "bad hook id");
+  auto& st = *registry()[id];
+  std::vector<std::pair<double, int64_t>> out;
+  for (auto& t : st.timed) {
+    t.stop.synchronize();
+    out.emplace_back((double)t.start.elapsed_time(t.stop) * 1e3, t.nbytes);
+  }
+  st.timed.clear();
+  return out;
+}
+
 int64_t buckets_seen(int64_t id) {
   TORCH_CHECK(id >= 0 && (size_t)id < registry().size(), "bad hook id");
   return registry()[id]->buckets;
@@ -147,4 +188,6 @@ int64_t buckets_seen(int64_t id) {
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("register_hook", &register_hook, "register the b2c comm hook on a c10d Reducer");
   m.def("buckets_seen", &buckets_seen);
+  m.def("enable_timing", &enable_timing);
+  m.def("collect_timing", &collect_timing);
 }

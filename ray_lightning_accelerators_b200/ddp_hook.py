@@ -44,7 +44,18 @@ class B2cHookState:
         self._side_used = False
 
     def enable_timing(self):
+        if getattr(self, "cpp_hook", None) is not None:
+            self.cpp_hook.enable_timing(self.cpp_hook_id, True)
         self.timing = []
+
+    def collect_timing_us(self):
+        """[(microseconds, bytes)] of every bucket allreduce since enable_timing(); synchronises."""
+        if getattr(self, "cpp_hook", None) is not None:
+            return [(us, nb) for us, nb in self.cpp_hook.collect_timing(self.cpp_hook_id)]
+        torch.cuda.synchronize()
+        out = [(e0.elapsed_time(e1) * 1e3, nb) for e0, e1, nb in (self.timing or [])]
+        self.timing = [] if self.timing is not None else None
+        return out
 
     def prepare(self, index, buf):
         comm = self.comm
