@@ -66,6 +66,26 @@ def test_train_single_worker(tmp_path):
     train_test(get_trainer(tmp_path, RayAccelerator(num_workers=1)), BoringModel())
 
 
+def test_predict(tmp_path):
+    """predict_test of the reference (tests/utils.py:137-152, test_ddp.py:99-115): after one short epoch on
+    2 workers the model the DRIVER holds classifies the test split with accuracy >= 0.5.  MNIST cannot be
+    downloaded here; the synthetic, MNIST-shaped digits of examples/mnist_module.py stand in."""
+    import torch
+    from torch.utils.data import DataLoader
+
+    from examples.mnist_module import MNISTClassifier, synthetic_mnist
+    torch.manual_seed(0)
+    model = MNISTClassifier({"layer_1": 32, "layer_2": 32, "lr": 1e-2, "batch_size": 32})
+    trainer = get_trainer(tmp_path, RayAccelerator(num_workers=2), limit_train_batches=10, limit_val_batches=2)
+    trainer.fit(model)
+    correct = total = 0
+    with torch.no_grad():
+        for x, y in DataLoader(synthetic_mnist(512, 7), batch_size=64):
+            correct += int((model(x).argmax(1) == y).sum())
+            total += len(y)
+    assert correct / total >= 0.5, f"accuracy {correct / total:.3f}"
+
+
 def test_early_stop(tmp_path):
     """constant val_loss + patience 2 stops a 500-epoch run early, on every worker at the same
     epoch (the stop flag is all-reduced on the control group, C9).  The reference pins
