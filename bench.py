@@ -93,23 +93,34 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return  # under torchrun only rank 0 works; the other ranks exit 0
+    # Under torch.distributed.run the environment carries the elastic agent's rendezvous
+    # (TORCHELASTIC_USE_AGENT_STORE=True makes a tcp:// init_process_group connect as a CLIENT to the
+    # agent's store, torch/distributed/rendezvous.py:188-196).  The gloo workers spawned below hold
+    # their own rendezvous on a fresh port, so every inherited coordinate has to go first.
+    for k in list(os.environ):
+        if k.startswith(("TORCHELASTIC_", "TORCH_NCCL_", "ROLE_", "GROUP_")) or k in (
+                "MASTER_ADDR", "MASTER_PORT", "RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE",
+                "GROUP_RANK", "GROUP_WORLD_SIZE", "OMP_NUM_THREADS"):
+            os.environ.pop(k)
     from oracle import gloo_ref
     cores = os.cpu_count() or 1
     world = max(1, args.gpus)
     threads = max(1, cores // world)
-    batch = args.ref_batch
+    batch = _ref_batch(args, world)
     steps = max(1, min(args.steps, args.ref_max_steps))
-    warmup = max(1, min(args.warmup, 2))
+    warmup = max(1, min(args.warmup, 1))
     r = gloo_ref.run_ddp(world, args.model, steps=steps, batch=batch, warmup=warmup, threads=threads,
                          distinct_batches=2, find_unused=True)
     sps = r["samples_per_sec"]
     sample = (f"{args.model} fp32, stock torch DDP over gloo, {world} worker(s) x {threads} thread(s), "
-              f"batch {batch}/worker (bounded sample of the 256/GPU workload), {steps} timed steps")
+              f"batch {batch}/worker (bounded sample: the GPU arm's 256/GPU workload at {batch * world} samples per step), "
+              f"{steps} timed steps after {warmup} warm-up")
     line = {
         "impl": "reference", "metric": "train_samples_per_sec", "value": sps, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": r["seconds"] / steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.model} synthetic 224x224 DDP (BASELINE configs[2]); CPU arm uses batch {batch}/worker",
+        "config": {"workload": f"{args.model} synthetic 224x224, SGD momentum, torch DDP 25 MB buckets (BASELINE configs[2]); "
+                               f"GPU arm batch {args.batch}/GPU, CPU reference arm batch {batch}/worker",
                    "global_batch": batch * world, "parallelism": f"dp{world}", "backend": "gloo"},
         "cpu_baseline": {"value": sps, "unit": "samples/s", "cores": threads * world, "kind": "reference",
                          "sample": sample, "host_cores": cores},
@@ -120,6 +131,12 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------- b2c arm (GPU)
+def _ref_batch(args, world):
+    """Per-worker batch of the CPU arm: the GPU arm's 256 images when one worker has the whole host,
+    256 // W with W workers, so that a step costs about the same host time at every N."""
+    return args.ref_batch if args.ref_batch > 0 else max(1, args.batch // max(1, world))
+
+
 def _build_worker(args, rank, world, local):
     """Worker set-up through the reference-facing plugin: the same RayAccelerator methods a Ray actor
     runs inside train_remote (ray_ddp.py:199-267), in the order PTL's ddp_train calls them."""
@@ -231,6 +248,8 @@ def run_b2c(args):
         grad_kernel, grad_path = f"k_allreduce_twoshot<f32,W={world}>", "libb2c.so: staged two-shot / one-shot through the arena"
     else:
         grad_kernel, grad_path = "k_scale_inplace<f32>", "libb2c.so: W=1 in-place scale pass (no peer)"
+    if stock:
+        grad_kernel, grad_path = "ncclDevKernel_AllReduce_*", "stock torch DDP: c10d Reducer + NCCL all_reduce (libb2c.so not on the gradient path)"
     per_bucket_us, n_timed = _bucket_stats(state) if (not stock and state.timing is not None) else ({}, 0)
     if not stock:
         state.timing = None
@@ -329,7 +348,8 @@ def run_b2c(args):
             "vs_baseline": None, "dtype": "f32" if args.wire != "bf16" else "f32 grads on a bf16 wire",
             "data": "synthetic",
             "config": {"workload": f"{args.model} synthetic 224x224, batch {batch}/GPU, SGD momentum, torch DDP 25 MB "
-                                   f"buckets via RayAccelerator(use_gpu=True) plugin methods (BASELINE configs[2])",
+                                   f"buckets via RayAccelerator(use_gpu=True) plugin methods (BASELINE configs[2]); "
+                                   f"the CPU reference arm (--impl reference) runs batch {_ref_batch(args, world)}/worker",
                        "global_batch": batch * world, "parallelism": f"dp{world}",
                        "l2": "inputs larger than L2 (activations of a 256-image batch >> 126 MB); no flush needed",
                        "grad_path": grad_path},
@@ -553,10 +573,11 @@ def _cpu_baseline(args):
     cores = os.cpu_count() or 1
     world = 2
     threads = max(1, cores // world)
-    r = gloo_ref.run_ddp(world, args.model, steps=2, batch=args.ref_batch, warmup=1, threads=threads, distinct_batches=1)
+    rb = args.ref_batch if args.ref_batch > 0 else 16
+    r = gloo_ref.run_ddp(world, args.model, steps=2, batch=rb, warmup=1, threads=threads, distinct_batches=1)
     return {"value": r["samples_per_sec"], "unit": "samples/s", "cores": world * threads, "host_cores": cores, "kind": "reference",
             "sample": f"{args.model} fp32, stock torch DDP over gloo (what RayAccelerator(use_gpu=False) runs, ray_ddp.py:227), "
-                      f"{world} workers x {threads} threads, batch {args.ref_batch}/worker, 2 timed steps after 1 warm-up"}
+                      f"{world} workers x {threads} threads, batch {rb}/worker, 2 timed steps after 1 warm-up"}
 
 
 def main():
@@ -572,7 +593,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--wire", default="f32", choices=["f32", "bf16"])
     ap.add_argument("--ar-iters", type=int, default=15)
-    ap.add_argument("--ref-batch", type=int, default=16)
+    ap.add_argument("--ref-batch", type=int, default=0, help="CPU reference arm: batch per worker (0 = batch // workers)")
     ap.add_argument("--ref-max-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-bucket-timing", action="store_true", help="no per-bucket CUDA events in the hook (host-bound tiny models)")

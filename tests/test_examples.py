@@ -33,6 +33,26 @@ def test_bench_reference_arm_contract():
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["cpu_baseline"]["kind"] == "reference"
 
 
+def test_bench_reference_arm_under_torchrun():
+    """The driver launches the reference arm like the GPU arm: under torch.distributed.run for N > 1.
+    Rank 0 alone works (its gloo workers hold their own rendezvous, the elastic agent's environment must
+    not leak into them); the other ranks exit 0; one JSON line, well inside a minute."""
+    import json
+    import time
+    t0 = time.time()
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29731", "bench.py", "--impl", "reference",
+                        "--gpus", "2", "--model", "mnist_mlp", "--steps", "2", "--warmup", "1"],
+                       cwd=ROOT, capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
+    lines = [ln for ln in p.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1, p.stdout
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0
+    assert "batch 128/worker" in line["config"]["workload"]
+    assert time.time() - t0 < 60
+
+
 def test_bench_gpu_arm_fails_loudly_without_cuda():
     import torch
     if torch.cuda.is_available():
