@@ -172,15 +172,138 @@ def _wrap(acc, model, args):
     from ray_lightning_accelerators_b200.ddp_hook import wrap_ddp
     wire = torch.bfloat16 if args.wire == "bf16" else None
     return wrap_ddp(model, acc.b2c_comm, device_ids=acc.get_device_ids(), wire_dtype=wire,
-                    find_unused_parameters=True)
+                    find_unused_parameters=True, reducer=args.reducer)
 
 
 def _bucket_stats(state):
-    """Per-launch device times recorded by the hook (Python or C++) around every b2c_allreduce of the timed region."""
+    """Per-launch device times recorded by the reducer / hook (CUDA events on the comm stream) around every b2c
+    launch of the timed region, averaged per bucket size."""
     by_size = {}
     for us, nbytes in state.collect_timing_us():
         by_size.setdefault(nbytes, []).append(us)
     return {nb: sum(v) / len(v) for nb, v in by_size.items()}, sum(len(v) for v in by_size.values())
+
+
+def _phase_split(comm, seq_bytes):
+    """Attribute the in-step time of each bucket launch with the kernels' own phase clock (channel 0,
+    %globaltimer): the ring keeps the last 32 kernels of the comm; `seq_bytes` is the per-step launch sequence
+    (bucket bytes, or None for a launch that is not a bucket).  Returns {bytes: (wait_for_peers_us, data_us, kernel_us)}."""
+    rows, total = comm.phase_ring_us()
+    L = len(seq_bytes)
+    if L == 0 or len(rows) < L:
+        return {}
+    steps = len(rows) // L
+    rows = rows[len(rows) - steps * L:]
+    acc = {}
+    for i, (to_a, a_to_b, b_to_end, _) in enumerate(rows):
+        nb = seq_bytes[i % L]
+        if nb is None:
+            continue
+        acc.setdefault(nb, []).append((to_a, a_to_b, to_a + a_to_b + b_to_end))
+    return {nb: tuple(sum(x[k] for x in v) / len(v) for k in range(3)) for nb, v in acc.items()}
+
+
+PARITY_SIZES = [12415000, 31500000, 29664000, 27021000, 1625000, 4 * 27883]  # ResNet-50 buckets + one ragged size
+
+
+def _parity_block(comm, rank, world, dev):
+    """Cross-GPU correctness where the driver can see it: outside the timed region, on the real bucket sizes.
+    b2c_allreduce(ALGO_AUTO) against torch.distributed all_reduce on a clone pre-divided by W (what the reference's
+    default hook computes, default_hooks.py:18-32), payload families int / randn / wide / special, fp32 and bf16;
+    b2c_broadcast against dist.broadcast for every root.  Bars are north_star's."""
+    import torch
+    import torch.distributed as dist
+    from ray_lightning_accelerators_b200.comm import ALGO_AUTO
+    names = {1: "oneshot", 2: "twoshot", 3: "nvls"}
+    rows, ok = [], True
+
+    def gen(kind, n, dtype):
+        g = torch.Generator(device=dev).manual_seed(4242 + 17 * rank + n % 1000)
+        if kind == "int":
+            x = torch.randint(-8, 9, (n,), generator=g, device=dev).float()
+        elif kind == "randn":
+            x = torch.randn(n, generator=g, device=dev)
+        elif kind == "wide":
+            x = torch.randn(n, generator=g, device=dev) * torch.exp2(torch.randint(-20, 20, (n,), generator=g, device=dev).float())
+        else:  # special values: zeros of both signs, infinities, NaN, denormals, large finite
+            base = torch.tensor([0.0, -0.0, float("inf"), float("-inf"), float("nan"), 1e-42, -1e-42, 3.0e37,
+                                 1.0, -1.0, 65504.0, 1.1754944e-38], device=dev)
+            x = base.repeat(n // base.numel() + 1)[:n].roll(rank % 2)
+        return x.to(dtype)
+
+    for dtype, tag in ((torch.float32, "f32"), (torch.bfloat16, "bf16")):
+        for S in PARITY_SIZES:
+            n = S // (4 if dtype == torch.float32 else 2)
+            for kind in ("int", "randn", "wide", "special"):
+                src = gen(kind, n, dtype)
+                ref = src.clone().div_(world)
+                dist.all_reduce(ref)
+                mag = src.float().abs() / world
+                dist.all_reduce(mag)                       # sum_r |g_r| / W: the error denominator
+                t = None
+                if comm.nvls_enabled:
+                    try:
+                        t = comm.nvls_empty(n, dtype)
+                    except MemoryError:
+                        t = None
+                arena = t is not None
+                if t is None:
+                    t = torch.empty(n, dtype=dtype, device=dev)
+                    comm.register(t)
+                t.copy_(src)
+                comm.allreduce(t, algo=ALGO_AUTO)
+                torch.cuda.synchronize()
+                comm.check_alive()
+                path = names[comm.stats()["last_algo"]]
+                got, want = t.float(), ref.float()
+                fin = torch.isfinite(want) & torch.isfinite(got) & (mag < 3.0e38)
+                err = float(((got - want).abs()[fin] / mag[fin].clamp_min(1.1754944e-38)).max().item()) if bool(fin.any()) else 0.0
+                nan_ok = bool((torch.isnan(got) == torch.isnan(want)).all())
+                inf_ok = bool((got[torch.isinf(want)] == want[torch.isinf(want)]).all())
+                bit = bool(torch.equal(t.view(torch.int16 if dtype == torch.bfloat16 else torch.int32),
+                                       ref.view(torch.int16 if dtype == torch.bfloat16 else torch.int32)))
+                rep = t.clone()
+                dist.broadcast(rep, src=0)
+                same = bool(torch.equal(rep.view(torch.int16 if dtype == torch.bfloat16 else torch.int32),
+                                        t.view(torch.int16 if dtype == torch.bfloat16 else torch.int32)))
+                bar = 1e-6 if dtype == torch.float32 else 2.0 ** -7   # fp32: 1e-6 of sum|g|/W; bf16: one ulp (2^-8 rel, + rounding)
+                good = same and nan_ok and inf_ok and (bit if kind == "int" else err <= bar)
+                flags = torch.tensor([0 if good else 1], device=dev)
+                dist.all_reduce(flags)
+                good = int(flags.item()) == 0
+                ok = ok and good
+                rows.append({"op": "allreduce", "dtype": tag, "bytes": S, "payload": kind, "path": path, "in_arena": arena,
+                             "max_rel_err": err, "bit_exact_vs_nccl": bit, "replicas_identical": same, "ok": good})
+                if arena:
+                    comm.nvls_free(t)
+                else:
+                    comm.deregister(t)
+    for S in (212904, 102441032):
+        for root in range(world):
+            g = torch.Generator(device=dev).manual_seed(9000 + rank)
+            src = torch.randint(0, 256, (S,), generator=g, device=dev, dtype=torch.uint8)
+            a, b = src.clone(), src.clone()
+            dist.broadcast(a, src=root)
+            m0 = comm.stats()["bcast_mc_launches"]
+            comm.broadcast(b, root=root)
+            torch.cuda.synchronize()
+            good = bool(torch.equal(a, b))
+            flags = torch.tensor([0 if good else 1], device=dev)
+            dist.all_reduce(flags)
+            good = int(flags.item()) == 0
+            ok = ok and good
+            rows.append({"op": "broadcast", "bytes": S, "root": root, "bytes_equal_vs_nccl": good,
+                         "path": "multicast" if comm.stats()["bcast_mc_launches"] > m0 else "pull", "ok": good})
+    summary = {}
+    for r in rows:
+        if r["op"] == "allreduce":
+            k = f'{r["dtype"]}/{r["path"]}'
+            summary[k] = max(summary.get(k, 0.0), r["max_rel_err"] if r["payload"] != "int" else 0.0)
+    return {"ok": ok, "checks": len(rows), "failed": [r for r in rows if not r["ok"]][:8],
+            "paths": sorted({r["path"] for r in rows}), "max_rel_err_by_dtype_and_path": summary,
+            "bars": "int payloads bit-exact vs NCCL; fp32 <= 1e-6 of sum|g|/W; bf16 <= 1 ulp; NaN/inf classes equal; "
+                    "replicas bitwise identical; broadcast byte-equal vs NCCL for every root",
+            "rows": [r for r in rows if r["bytes"] in (31500000, 102441032) and r.get("payload", "randn") == "randn"]}
 
 
 def run_b2c(args):
@@ -197,11 +320,16 @@ def run_b2c(args):
         raise SystemExit("bench.py (b2c arm) needs a CUDA device; there is no CPU fallback. "
                          "Use --impl reference for the reference's CPU path.")
     torch.backends.cudnn.benchmark = True
-    # room in the multicast arena for the allreduce section's buffers as well (bump allocator, never freed)
+    # room in the multicast arena for the parity / allreduce sections' buffers as well
     os.environ.setdefault("B2C_NVLS_ARENA_BYTES", str(2 << 30))
     acc, model, ddp, opt = _build_worker(args, rank, world, local)
     stock = args.impl == "nccl"
     comm, state = acc.b2c_comm, (None if stock else ddp._b2c_state)
+    own = (not stock) and hasattr(ddp, "fuse_optimizer")
+    fused = False
+    if own and args.fused_opt:
+        opt = ddp.fuse_optimizer(opt)
+        fused = type(opt).__name__ == "FusedOptimizer"
     dev = torch.device("cuda", torch.cuda.current_device())
     batch = args.batch
     K, W = args.steps, max(3, args.warmup)
@@ -240,19 +368,34 @@ def run_b2c(args):
     clocks = sampler.stop() if rank == 0 else None
     st1 = comm.stats()
     launches = st1["launches"] - launches0
+    opt_name = type(getattr(opt, "_opt", opt)).__name__
+    what = f"gradient average + {opt_name} step in one launch per bucket (weights travel back)" if fused else "gradient allreduce"
     if st1["nvls_launches"] > st0["nvls_launches"]:
-        grad_kernel, grad_path = "k_allreduce_nvls<f32>", "libb2c.so: NVLS in-switch reduction, DDP buckets inside the multicast arena (in place)"
+        grad_kernel = "k_fused_step_nvls<SGD>" if fused else "k_nvls_inplace<f32>"
+        grad_path = f"libb2c.so: {what}; in-switch reduction (multimem), buckets inside the multicast arena, in place"
     elif st1["zerocopy_launches"] > st0["zerocopy_launches"]:
-        grad_kernel, grad_path = f"k_allreduce_twoshot_zc<f32,W={world}>", "libb2c.so: zero-copy two-shot on registered DDP buckets"
+        grad_kernel = f"k_fused_step_zc<SGD,W={world}>" if fused else f"k_allreduce_twoshot_zc<f32,W={world}>"
+        grad_path = f"libb2c.so: {what}; zero-copy two-shot over peer-mapped buckets"
     elif world > 1:
         grad_kernel, grad_path = f"k_allreduce_twoshot<f32,W={world}>", "libb2c.so: staged two-shot / one-shot through the arena"
+    elif fused:
+        grad_kernel, grad_path = "k_fused_step_local<SGD>", f"libb2c.so: {opt_name} step over the gradient buckets (W=1: no peer to reduce with)"
     else:
-        grad_kernel, grad_path = "k_scale_inplace<f32>", "libb2c.so: W=1 in-place scale pass (no peer)"
+        grad_kernel, grad_path = None, "W=1 and no fused step: nothing for libb2c.so to do inside a step"
     if stock:
         grad_kernel, grad_path = "ncclDevKernel_AllReduce_*", "stock torch DDP: c10d Reducer + NCCL all_reduce (libb2c.so not on the gradient path)"
     per_bucket_us, n_timed = _bucket_stats(state) if (not stock and state.timing is not None) else ({}, 0)
     if not stock:
         state.timing = None
+    # device-side attribution of the in-step launches (own reducer: the per-step launch sequence is known)
+    phases = {}
+    if own and world > 1:
+        seq = ([None] if (ddp.bufsync.flat is not None and not getattr(ddp, "_c4_folded", False)) else []) + \
+              [b.nbytes for b in ddp.reducer.buckets]
+        try:
+            phases = _phase_split(comm, seq)
+        except Exception as e:  # noqa: BLE001
+            phases = {"error": str(e)[:120]}
     ms_total = float(ms.item())
     value = world * batch * K / (ms_total / 1e3)
 
@@ -304,17 +447,18 @@ def run_b2c(args):
 
     # ---- roofline of the dominant b2c kernel of the timed region (largest share of our device time)
     peaks, peak_kind = _peaks()
-    total_us = {nb: us * 1.0 for nb, us in per_bucket_us.items()}
-    dom = max(total_us, key=lambda nb: total_us[nb]) if total_us else None
+    dom = max(per_bucket_us, key=lambda nb: per_bucket_us[nb]) if per_bucket_us else None
     roofline = None
     if dom is not None:
         us = per_bucket_us[dom]
         if world == 1:
-            alg = 2.0 * dom  # read S, write S (W = 1: scale pass in place)
+            # fused SGD+momentum step, local: read g, w, m and write w, m = 20 bytes per fp32 parameter
+            alg = 5.0 * dom
             roofline = {"bound": "hbm", "kernel": grad_kernel, "achieved": alg / us / 1e3,
                         "peak": peaks["hbm_gbs"], "peak_kind": f"{peak_kind} HBM copy", "unit": "GB/s",
                         "frac": alg / us / 1e3 / peaks["hbm_gbs"], "traffic": None,
-                        "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom}
+                        "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom,
+                        "note": "in-step: the kernel shares the GPU with the tail of backward"}
         else:
             alg = 2.0 * (world - 1) / world * dom  # NVLink bytes per GPU per direction (busbw numerator)
             roofline = {"bound": "nvlink", "kernel": grad_kernel,
@@ -322,21 +466,34 @@ def run_b2c(args):
                         "peak_kind": "nominal NVLink 5 per direction (measured peer copy 770 GB/s)", "unit": "GB/s",
                         "frac": alg / us / 1e3 / NVLINK_NOMINAL_GBPS,
                         "frac_of_measured_copy": alg / us / 1e3 / NVLINK_MEASURED_COPY_GBPS, "traffic": None,
-                        "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom}
+                        "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom,
+                        "note": "in-step event time: includes the wait for the slowest rank at the entry barrier "
+                                "(see grad_buckets[*].wait_for_peers_us) and for a free SM"}
+            if dom in phases and isinstance(phases[dom], tuple):
+                data_us = phases[dom][1]
+                roofline["data_phase_us"] = data_us
+                roofline["frac_data_phase"] = alg / data_us / 1e3 / NVLINK_NOMINAL_GBPS if data_us > 0 else None
     if roofline is not None:
-        try:  # per-launch DRAM bytes of this kernel from the committed ncu --set full capture
-            with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as f:
+        try:  # per-launch DRAM bytes of this kernel from the committed ncu capture
+            with open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")) as f:
                 cap = json.load(f).get(roofline["kernel"])
             if cap:
                 roofline["traffic"] = cap["dram_bytes_read"] + cap["dram_bytes_write"]
-                roofline["traffic_note"] = (f"ncu --set full, isolated launch on a {cap['bucket_bytes']} B bucket "
-                                            "(results still L2-resident at kernel end, so DRAM writes are not counted)")
+                roofline["traffic_note"] = cap.get("note")
         except Exception:
             pass
-    buckets = [{"bytes": nb, "us": per_bucket_us[nb],
-                "busbw_GBps": (2.0 * (world - 1) / world * nb / per_bucket_us[nb] / 1e3) if world > 1 else None}
-               for nb in sorted(per_bucket_us)]
+    buckets = []
+    for nb in sorted(per_bucket_us):
+        row = {"bytes": nb, "us": per_bucket_us[nb],
+               "busbw_GBps": (2.0 * (world - 1) / world * nb / per_bucket_us[nb] / 1e3) if world > 1 else None}
+        if nb in phases and isinstance(phases[nb], tuple):
+            wait, data, kern = phases[nb]
+            row.update({"wait_for_peers_us": wait, "data_phase_us": data, "kernel_us": kern,
+                        "queue_and_launch_us": per_bucket_us[nb] - kern,
+                        "busbw_data_phase_GBps": 2.0 * (world - 1) / world * nb / data / 1e3 if data > 0 else None})
+        buckets.append(row)
 
+    parity = _parity_block(comm, rank, world, dev) if (world > 1 and not stock and not args.no_parity) else None
     allreduce = _allreduce_section(args, comm, rank, world, dev) if not stock else None
     cpu_baseline = _cpu_baseline(args) if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
 
@@ -347,16 +504,17 @@ def run_b2c(args):
             "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32" if args.wire != "bf16" else "f32 grads on a bf16 wire",
             "data": "synthetic",
-            "config": {"workload": f"{args.model} synthetic 224x224, batch {batch}/GPU, SGD momentum, torch DDP 25 MB "
+            "config": {"workload": f"{args.model} synthetic 224x224, batch {batch}/GPU, SGD momentum, 25 MB gradient "
                                    f"buckets via RayAccelerator(use_gpu=True) plugin methods (BASELINE configs[2]); "
                                    f"the CPU reference arm (--impl reference) runs batch {_ref_batch(args, world)}/worker",
                        "global_batch": batch * world, "parallelism": f"dp{world}",
                        "l2": "inputs larger than L2 (activations of a 256-image batch >> 126 MB); no flush needed",
-                       "grad_path": grad_path},
+                       "reducer": "torch c10d Reducer + NCCL" if stock else ("b2c (own bucket reducer)" if own else "torch c10d Reducer + b2c comm hook"),
+                       "fused_optimizer": fused, "grad_path": grad_path},
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": float(ms2.item()) / K, "last_loss": last},
             "gpu_launches": int(launches), "b2c_launches_timed": int(n_timed),
-            "clocks": clocks, "roofline": roofline, "grad_buckets": buckets, "allreduce": allreduce,
+            "clocks": clocks, "roofline": roofline, "grad_buckets": buckets, "parity": parity, "allreduce": allreduce,
         }
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
@@ -365,6 +523,8 @@ def run_b2c(args):
     from ray_lightning_accelerators_b200.ray_ddp import _close_worker_comm
     _close_worker_comm()
     dist.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        raise SystemExit("parity block failed: see the 'parity' object of the JSON line")
 
 
 # ---------------------------------------------------------------------------- Horovod-style arm
@@ -490,7 +650,7 @@ def _allreduce_section(args, comm, rank, world, dev):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.sort().values[len(ts) // 2])
 
-    def pipelined(make, fn, S):
+    def pipelined(make, fn, S, free=None):
         """Back-to-back launches over distinct buffers whose total footprint exceeds L2 (no flush
         needed): launch latency and barrier skew overlap with the previous kernel, as they do for the
         buckets of a real backward pass.  One event pair around 3 rounds; per-allreduce time."""
@@ -511,6 +671,9 @@ def _allreduce_section(args, comm, rank, world, dev):
         t = torch.tensor([a.elapsed_time(b_) * 1e3 / (3 * k)], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if free is not None:
+            for b in reversed(bufs):
+                free(b)
         return float(t.item())
 
     if world > 1:
@@ -544,12 +707,21 @@ def _allreduce_section(args, comm, rank, world, dev):
                     t_ = torch.randn(S // 4, device=dev)
                     comm.register(t_)
                     return t_
-                up = pipelined(make, lambda t_: comm.allreduce(t_, algo=ALGO_AUTO), S)
+                def free(t_):
+                    if comm.in_nvls_arena(t_):
+                        comm.nvls_free(t_)
+                    else:
+                        comm.deregister(t_)
+                up = pipelined(make, lambda t_: comm.allreduce(t_, algo=ALGO_AUTO), S, free)
                 un = pipelined(lambda: torch.randn(S // 4, device=dev), lambda t_: dist.all_reduce(t_), S)
                 row.update({"us_pipelined": up, "busbw_pipelined_GBps": bus / up / 1e3,
                             "frac_of_900_pipelined": bus / up / 1e3 / NVLINK_NOMINAL_GBPS,
                             "nccl_us_pipelined": un, "nccl_busbw_pipelined_GBps": bus / un / 1e3})
             out.append(row)
+            if comm.in_nvls_arena(x):
+                comm.nvls_free(x)
+            else:
+                comm.deregister(x)
         return {"mode": f"nvlink W={world}",
                 "timing": "us: median of %d isolated launches, L2 flushed, ranks aligned, max over ranks; "
                           "us_pipelined: back-to-back launches over distinct buffers > L2, max over ranks" % iters,
@@ -596,6 +768,12 @@ def main():
     ap.add_argument("--ref-batch", type=int, default=0, help="CPU reference arm: batch per worker (0 = batch // workers)")
     ap.add_argument("--ref-max-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--reducer", default="b2c", choices=["b2c", "torch"],
+                    help="b2c: own bucket reducer (default); torch: c10d Reducer with the b2c comm hook")
+    ap.add_argument("--fused-opt", dest="fused_opt", action="store_true", default=True,
+                    help="fold optimizer.step() into the bucket launches (default with the own reducer)")
+    ap.add_argument("--no-fused-opt", dest="fused_opt", action="store_false")
+    ap.add_argument("--no-parity", action="store_true", help="skip the cross-GPU parity block (N > 1)")
     ap.add_argument("--no-bucket-timing", action="store_true", help="no per-bucket CUDA events in the hook (host-bound tiny models)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -71,7 +71,19 @@ enum {
   B2C_PARAM_MAX_BLOCKS_NVLS = 10,
   B2C_PARAM_UNROLL_NVLS = 11,     /* multimem.ld_reduce vectors in flight per thread: 2, 4, 8 or 16 */
   B2C_PARAM_UNROLL_ZC = 12,       /* zero-copy two-shot, W = 8 only: 0 (default 2), 1, 2 or 4 vectors per peer in flight */
-  B2C_PARAM__COUNT = 13
+  B2C_PARAM_PDL = 13,             /* 1 (default): the lean NVLS kernel is launched with programmatic stream
+                                     serialization, so a train of bucket allreduces overlaps launch with drain */
+  B2C_PARAM_THREADS_NVLS = 14,    /* lean NVLS kernel: 512 (default) or 256 threads per CTA (the 256-thread
+                                     build stays within 64 registers and fits beside backward kernels) */
+  B2C_PARAM_NVLS_STAGE_BYTES = 15, /* size of one of the two multicast staging slots, carved out of the arena
+                                     on first use (tensors outside the arena, multicast broadcast) */
+  B2C_PARAM_NVLS_LEAN = 16,       /* 1 (default): in-place NVLS uses the lean kernel (multicast flag barrier);
+                                     0: the round-1 kernel (unicast flags), kept for A/B measurements */
+  B2C_PARAM_BCAST_MC = 17,        /* 1 (default): with the multicast arena up b2c_broadcast goes through the
+                                     switch (root sends its bytes once); 0: every rank pulls from the root */
+  B2C_PARAM_MC_ACQ_POLL = 18,     /* multicast flag barrier: 1 (default) spin with ld.acquire.sys, 0 spin relaxed
+                                     and fence once at the end (a measurement knob) */
+  B2C_PARAM__COUNT = 19
 };
 
 /* error codes */
@@ -102,6 +114,9 @@ typedef struct b2c_stats {
   uint32_t device_status;       /* 0, or the sticky error code the kernels reported */
   uint32_t device_status_detail[3]; /* epoch, block, peer at failure */
   uint32_t reserved;
+  uint64_t bcast_mc_launches;   /* broadcasts that went through the switch (multimem.st) */
+  uint64_t noop_calls;          /* allreduce calls answered without a launch (world 1, scale 1) */
+  uint64_t fused_steps;         /* b2c_fused_step calls */
 } b2c_stats;
 
 /* ---- library ---------------------------------------------------------- */
@@ -199,16 +214,52 @@ int b2c_nvls_export(b2c_comm* comm, size_t bytes, void* blob, size_t* len);
 int b2c_nvls_import(b2c_comm* comm, const void* blobs, size_t len_each);
 int b2c_nvls_bind(b2c_comm* comm);
 int b2c_nvls_arena(b2c_comm* comm, void** base, size_t* bytes);
-/* Bump allocation inside the arena (256-byte aligned, same sequence on every rank => same offsets).
+/* Allocation inside the arena: first fit with coalescing, 256-byte aligned, deterministic — ranks that
+ * issue the same sequence of b2c_nvls_alloc / b2c_nvls_free calls get the same offsets, which is what
+ * the in-place kernels need.  The first 64 KiB of the arena hold the multicast flag counters.
  * b2c_nvls_pool_bind makes this comm's arena the backing store of b2c_pool_alloc / b2c_pool_free,
- * which have the signature torch.cuda.memory.CUDAPluggableAllocator expects: DDP built inside a
- * torch.cuda.MemPool on that allocator gets its gradient buckets INSIDE the multicast arena, so the
- * per-step allreduce is the in-place NVLS kernel with no staging at all.  Frees are LIFO roll-backs
- * or no-ops (the buckets live as long as the comm). */
+ * which have the signature torch.cuda.memory.CUDAPluggableAllocator expects: tensors allocated inside a
+ * torch.cuda.MemPool on that allocator live INSIDE the multicast arena, so the per-step allreduce is
+ * the in-place NVLS kernel with no staging at all. */
 int b2c_nvls_alloc(b2c_comm* comm, size_t bytes, void** ptr);
+int b2c_nvls_free(b2c_comm* comm, void* ptr);
 int b2c_nvls_pool_bind(b2c_comm* comm);
 void* b2c_pool_alloc(ptrdiff_t size, int device, b2c_stream_t stream);
 void b2c_pool_free(void* ptr, ptrdiff_t size, int device, b2c_stream_t stream);
+
+/* ---- fused optimizer step -------------------------------------------------
+ * the step on the far side of the path.  What the reference reaches after the gradient
+ * allreduce — optimizer.step() inside the PTL train loop entered at ray_ddp.py:218-219 / ray_horovod.py:159 —
+ * is folded into the reduction: the rank that reduces shard r of a gradient bucket applies the optimizer to
+ * shard r (fp32 state for the owned shard only: each rank holds 1/W of the momentum / Adam moments) and the
+ * updated WEIGHTS are written into every rank's parameter bucket.  Arithmetic follows torch.optim.SGD / Adam /
+ * AdamW operation by operation in fp32 (the gradient average is the allreduce contract above).
+ *   grad / param : flat fp32 buckets of `count` elements with the same layout, both inside the multicast arena
+ *                  (in-switch path) or both registered with every peer (peer-to-peer path), 16-byte aligned,
+ *                  count % 4 == 0 when world > 1.  `grad` is left untouched; `param` is updated on every rank.
+ *   state1/2     : fp32, b2c_fused_shard() elements each, this rank's shard only, zero-initialised by the caller
+ *                  (SGD: momentum buffer / unused; Adam: exp_avg / exp_avg_sq).
+ *   bcast_*      : optional C4 fold (multicast arena only): `bcast_bytes` (multiple of 16) at `bcast_buf` inside
+ *                  the arena are replicated from rank `bcast_root` in the same launch — the per-forward module
+ *                  buffer broadcast (_sync_buffers) without a launch of its own.
+ * No reference counterpart as an entry point (the reference calls the optimizer in Python). */
+enum { B2C_OPT_KIND_SGD = 1, B2C_OPT_KIND_ADAM = 2, B2C_OPT_KIND_ADAMW = 3 };
+typedef struct b2c_opt {
+  int kind;                 /* B2C_OPT_KIND_* */
+  int nesterov;             /* SGD */
+  int first_step;           /* SGD with momentum: 1 on the first step (buf = grad, as torch creates it) */
+  /* hyper-parameters in double, as the Python optimizers hold them: every derived scalar (1 - beta2, lr /
+   * bias_correction1, ...) is formed in double and rounded to float once, like torch's own kernels get them */
+  double lr, momentum, dampening, weight_decay;
+  double beta1, beta2, eps; /* Adam / AdamW */
+  double bias_correction1;  /* 1 - beta1^t */
+  double bias_correction2;  /* 1 - beta2^t */
+} b2c_opt;
+int b2c_fused_shard(size_t count, int world, int rank, size_t* first_elem, size_t* n_elems);
+int b2c_fused_step(b2c_comm* comm, void* grad, void* param, size_t count, int dtype, float scale, const b2c_opt* opt,
+                   void* state1, void* state2, void* bcast_buf, size_t bcast_bytes, int bcast_root, b2c_stream_t stream);
+int b2c_group_fused_step(b2c_comm** comms, void** grads, void** params, size_t count, int dtype, float scale,
+                         const b2c_opt* opt, void** state1, void** state2, b2c_stream_t stream);
 
 /* ---- allocation-free variant ----------------------------------------------
  * No counterpart in the reference.
@@ -232,6 +283,14 @@ void b2c_pool_free(void* ptr, ptrdiff_t size, int device, b2c_stream_t stream);
 #define B2C_NOALLOC_MAX_BYTES (256 * 1024)
 int b2c_allreduce_local_noalloc(void* const* bufs, int world, size_t count, int dtype, float scale,
                                 b2c_stream_t stream);
+/* The call above only enqueues, so it cannot itself report that its kernel gave up waiting in the flag
+ * barrier (2 s; with a cooperative launch this means the GPU was taken away mid-kernel).  The kernel
+ * records that in four sticky words next to the scratch array — error code, epoch, channel, virtual
+ * rank waited for — which no later call wipes.  b2c_noalloc_status waits for the current device, copies
+ * them to out[4] (may be NULL), returns B2C_OK when they are clear and B2C_ETIMEOUT otherwise (the
+ * buffers of the failing call were left unreduced); reset != 0 clears them.  Allocates nothing.
+ * No counterpart in the reference. */
+int b2c_noalloc_status(uint32_t out[4], int reset);
 
 /* ---- knobs, counters, introspection ------------------------------------ */
 int b2c_set_param(b2c_comm* comm, int key, long value);
@@ -244,6 +303,11 @@ int b2c_comm_info(b2c_comm* comm, int* rank, int* world, int* device);
  * out[0] kernel start, out[1] passed barrier A, out[2] passed barrier B, out[3] end.
  * Synchronises the device; a profiling aid, not for the hot path. */
 int b2c_get_phase_ns(b2c_comm* comm, uint64_t out[4]);
+/* The same four stamps for the last (up to 32) kernels of this comm, oldest first, 4 x u64 each, so a
+ * whole training step can be attributed bucket by bucket afterwards: start->A is the wait for the
+ * slowest rank, A->B the data phase.  Returns the number of entries written (<= max_entries) or a
+ * negative error; *total = kernels stamped since the comm was created.  Synchronises the device. */
+int b2c_get_phase_ring(b2c_comm* comm, uint64_t* out, int max_entries, uint32_t* total);
 
 #ifdef __cplusplus
 }

@@ -173,3 +173,46 @@ def bf16_ulp_diff(a_bits, b_bits):
         x = np.asarray(x, np.uint16).astype(np.int32)
         return np.where(x & 0x8000, 0x8000 - x, x)  # negative values mirror below zero
     return np.abs(key(a_bits) - key(b_bits))
+
+
+# ------------------------------------------------------------------ fused optimizer step (restatement)
+def _f32(x):
+    return np.asarray(x, dtype=np.float32)
+
+
+def _fma(a, b, c):
+    """fp32 fused multiply-add: the product of two fp32 values is exact in fp64."""
+    return (a.astype(np.float64) * np.float64(b) + c.astype(np.float64)).astype(np.float32)
+
+
+def fused_step_f32(kind, cfg, t, g, w, s1, s2):
+    """CPU restatement of libb2c.so's optimizer epilogue (csrc/b2c_kernels.cuh: opt_apply), which follows
+    torch.optim.SGD / Adam / AdamW (single-tensor form) operation by operation in fp32.  Pinned against the real
+    torch optimizers by tests/test_oracle.py.  g: averaged gradient; w, s1, s2: fp32 arrays, updated in place;
+    t: 1-based step count.  Scalars are formed in double and rounded to fp32 once, as the host side does."""
+    g, lr, wd = _f32(g).copy(), cfg["lr"], cfg.get("weight_decay", 0.0)
+    if kind == "sgd":
+        mom, damp = cfg.get("momentum", 0.0), cfg.get("dampening", 0.0)
+        if wd != 0.0:
+            g = _fma(w, np.float32(wd), g)
+        if mom != 0.0:
+            if t == 1:
+                s1[:] = g
+            else:
+                s1[:] = _fma(g, np.float32(1.0 - damp), (s1 * np.float32(mom)).astype(np.float32))
+            g = _fma(s1, np.float32(mom), g) if cfg.get("nesterov", False) else s1
+        w[:] = _fma(g, np.float32(-lr), w)
+        return w
+    b1, b2 = cfg["betas"]
+    if kind == "adamw":
+        w[:] = w * np.float32(1.0 - lr * wd)
+    elif wd != 0.0:
+        g = _fma(w, np.float32(wd), g)
+    s1[:] = _fma((g - s1).astype(np.float32), np.float32(1.0 - b1), s1)
+    s2[:] = ((g * np.float32(1.0 - b2)).astype(np.float32).astype(np.float64) * g.astype(np.float64) +
+             (s2 * np.float32(b2)).astype(np.float32).astype(np.float64)).astype(np.float32)
+    step_size = np.float32(lr / (1.0 - b1 ** t))
+    bc2_sqrt = np.float32(np.sqrt(1.0 - b2 ** t))
+    denom = (np.sqrt(s2).astype(np.float32) / bc2_sqrt).astype(np.float32) + np.float32(cfg["eps"])
+    w[:] = _fma((s1 / denom).astype(np.float32), -step_size, w)
+    return w

@@ -30,6 +30,13 @@ PARAM_NVLS_MIN_BYTES = 9
 PARAM_MAX_BLOCKS_NVLS = 10
 PARAM_UNROLL_NVLS = 11
 PARAM_UNROLL_ZC = 12
+PARAM_PDL = 13
+PARAM_THREADS_NVLS = 14
+PARAM_NVLS_STAGE_BYTES = 15
+PARAM_NVLS_LEAN = 16
+PARAM_BCAST_MC = 17
+PARAM_MC_ACQ_POLL = 18
+PHASE_RING = 32
 REG_BLOB_BYTES = 128
 NVLS_BLOB_BYTES = 64
 NOALLOC_MAX_BYTES = 256 * 1024
@@ -51,6 +58,17 @@ class B2cError(RuntimeError):
         self.code = code
 
 
+OPT_SGD, OPT_ADAM, OPT_ADAMW = 1, 2, 3
+
+
+class Opt(ctypes.Structure):
+    """b2c_opt of include/b2c.h."""
+    _fields_ = [("kind", ctypes.c_int), ("nesterov", ctypes.c_int), ("first_step", ctypes.c_int),
+                ("lr", ctypes.c_double), ("momentum", ctypes.c_double), ("dampening", ctypes.c_double),
+                ("weight_decay", ctypes.c_double), ("beta1", ctypes.c_double), ("beta2", ctypes.c_double),
+                ("eps", ctypes.c_double), ("bias_correction1", ctypes.c_double), ("bias_correction2", ctypes.c_double)]
+
+
 class Stats(ctypes.Structure):
     _fields_ = [
         ("calls_allreduce", ctypes.c_uint64),
@@ -69,6 +87,9 @@ class Stats(ctypes.Structure):
         ("device_status", ctypes.c_uint32),
         ("device_status_detail", ctypes.c_uint32 * 3),
         ("reserved", ctypes.c_uint32),
+        ("bcast_mc_launches", ctypes.c_uint64),
+        ("noop_calls", ctypes.c_uint64),
+        ("fused_steps", ctypes.c_uint64),
     ]
 
     def as_dict(self):
@@ -105,15 +126,21 @@ SIGNATURES = {
     "b2c_nvls_bind": (_int, [_vp]),
     "b2c_nvls_arena": (_int, [_vp, _pp, _c.POINTER(_sz)]),
     "b2c_nvls_alloc": (_int, [_vp, _sz, _pp]),
+    "b2c_nvls_free": (_int, [_vp, _vp]),
     "b2c_nvls_pool_bind": (_int, [_vp]),
     "b2c_pool_alloc": (_vp, [_c.c_ssize_t, _int, _vp]),
     "b2c_pool_free": (None, [_vp, _c.c_ssize_t, _int, _vp]),
+    "b2c_fused_shard": (_int, [_sz, _int, _int, _c.POINTER(_sz), _c.POINTER(_sz)]),
+    "b2c_fused_step": (_int, [_vp, _vp, _vp, _sz, _int, _c.c_float, _c.POINTER(Opt), _vp, _vp, _vp, _sz, _int, _vp]),
+    "b2c_group_fused_step": (_int, [_pp, _pp, _pp, _sz, _int, _c.c_float, _c.POINTER(Opt), _pp, _pp, _vp]),
     "b2c_allreduce_local_noalloc": (_int, [_pp, _int, _sz, _int, _c.c_float, _vp]),
+    "b2c_noalloc_status": (_int, [_c.POINTER(_c.c_uint32 * 4), _int]),
     "b2c_set_param": (_int, [_vp, _int, _c.c_long]),
     "b2c_get_param": (_int, [_vp, _int, _c.POINTER(_c.c_long)]),
     "b2c_get_stats": (_int, [_vp, _c.POINTER(Stats)]),
     "b2c_comm_arena": (_int, [_vp, _pp, _c.POINTER(_sz)]),
     "b2c_get_phase_ns": (_int, [_vp, _c.POINTER(_c.c_uint64 * 4)]),
+    "b2c_get_phase_ring": (_int, [_vp, _c.POINTER(_c.c_uint64), _int, _c.POINTER(_c.c_uint32)]),
     "b2c_comm_info": (_int, [_vp, _c.POINTER(_int), _c.POINTER(_int), _c.POINTER(_int)]),
 }
 

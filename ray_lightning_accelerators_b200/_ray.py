@@ -388,7 +388,3 @@ class Queue:
 def shutdown():
     for a in list(_live_actors):
         kill(a)
-
-
-def is_real_ray():
-    return False

@@ -31,6 +31,13 @@ _ENV_PARAMS = {
     "B2C_ZEROCOPY_MIN_BYTES": _lib.PARAM_ZEROCOPY_MIN_BYTES,
     "B2C_NVLS_MIN_BYTES": _lib.PARAM_NVLS_MIN_BYTES,
     "B2C_MAX_BLOCKS_NVLS": _lib.PARAM_MAX_BLOCKS_NVLS,
+    "B2C_UNROLL_NVLS": _lib.PARAM_UNROLL_NVLS,
+    "B2C_THREADS_NVLS": _lib.PARAM_THREADS_NVLS,
+    "B2C_PDL": _lib.PARAM_PDL,
+    "B2C_NVLS_LEAN": _lib.PARAM_NVLS_LEAN,
+    "B2C_BCAST_MC": _lib.PARAM_BCAST_MC,
+    "B2C_MC_ACQ_POLL": _lib.PARAM_MC_ACQ_POLL,
+    "B2C_NVLS_STAGE_BYTES": _lib.PARAM_NVLS_STAGE_BYTES,
 }
 
 
@@ -57,6 +64,12 @@ def _check_tensor(t):
         raise ValueError("b2c operates on CUDA tensors only (there is no CPU path)")
     if not t.is_contiguous():
         raise ValueError("b2c needs a contiguous tensor (DDP buckets are flat 1-D)")
+
+
+def fused_shard(lib, count, world, rank):
+    first, n = ctypes.c_size_t(), ctypes.c_size_t()
+    _lib.check(lib.b2c_fused_shard(int(count), int(world), int(rank), ctypes.byref(first), ctypes.byref(n)))
+    return first.value, n.value
 
 
 class _Base:
@@ -86,6 +99,23 @@ class _Base:
         if t[2] < t[1]:  # kernels with a single barrier (one-shot, broadcast) leave slot 2 stale
             t[2] = t[3]
         return ((t[1] - t[0]) / 1e3, (t[2] - t[1]) / 1e3, (t[3] - t[2]) / 1e3)
+
+    def phase_ring_us(self):
+        """[(start->A, A->B, B->end, start_ns)] of this comm's last (up to 32) kernels, oldest first, in
+        microseconds (synchronises).  start->A is the wait for the slowest rank, A->B the data phase."""
+        n = _lib.PHASE_RING
+        out = (ctypes.c_uint64 * (4 * n))()
+        total = ctypes.c_uint32()
+        got = self._lib.b2c_get_phase_ring(self._first, out, n, ctypes.byref(total))
+        if got < 0:
+            _lib.check(got)
+        rows = []
+        for i in range(got):
+            t = [out[4 * i + k] for k in range(4)]
+            if t[2] < t[1]:
+                t[2] = t[3]
+            rows.append(((t[1] - t[0]) / 1e3, (t[2] - t[1]) / 1e3, (t[3] - t[2]) / 1e3, t[0]))
+        return rows, total.value
 
     def check_alive(self):
         """Raise if a kernel reported a flag-barrier timeout (sticky)."""
@@ -128,13 +158,29 @@ class Comm(_Base):
         W x 256 bytes, once).  ray_lightning/ray_ddp.py:232-237 creates that group."""
         import torch.distributed as dist
         rank, world = dist.get_rank(group), dist.get_world_size(group)
+        # Handle exchanges may happen later than set-up and from another thread (a DDP comm hook registers a
+        # bucket the first time it sees it, on the autograd thread, while the main thread is free to issue
+        # its own collectives).  They therefore never share a communicator with the training loop: when the
+        # group is NCCL a private gloo group carries the blobs (created here, collectively, on the main thread).
+        side = group
+        if world > 1 and dist.get_backend(group) != "gloo":
+            ranks = dist.get_process_group_ranks(group) if group is not None else None
+            side = dist.new_group(ranks=ranks, backend="gloo")
 
         def exchange(blob):
             out = [None] * world
-            dist.all_gather_object(out, blob, group=group)
+            dist.all_gather_object(out, blob, group=side)
             return out
 
         return cls(rank, world, device=device, arena_bytes=arena_bytes, exchange=exchange)
+
+    @property
+    def side_stream(self):
+        """THE high-priority stream of this comm for reductions that overlap backward.  One per comm: calls on
+        a comm must be stream-ordered, so every user (DDP reducer, hvd optimizers) shares it."""
+        if getattr(self, "_side_stream", None) is None:
+            self._side_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        return self._side_stream
 
     def export(self):
         buf = ctypes.create_string_buffer(_lib.EXPORT_BLOB_BYTES)
@@ -156,18 +202,24 @@ class Comm(_Base):
         keeps working either way."""
         _check_tensor(t)
         key = (t.data_ptr(), t.numel() * t.element_size())
-        if key in self._registered:
-            return self._registered[key]
         if self.world == 1:
             self._registered[key] = False
             return False
+        # ALWAYS collective: a rank-local cache hit must not skip the exchange (the same address can be a
+        # fresh allocation on a peer).  The hit/miss flag travels with the blob; unless every rank has this
+        # exact buffer registered already, everyone drops what it has and maps the current buffers.
+        cached = key in self._registered
         buf = ctypes.create_string_buffer(_lib.REG_BLOB_BYTES)
         n = ctypes.c_size_t(_lib.REG_BLOB_BYTES)
         rc = self._lib.b2c_register_export(self._h, ctypes.c_void_p(key[0]), key[1], buf, ctypes.byref(n))
-        blobs = self._exchange(buf.raw if rc == 0 else None)
-        ok = all(b is not None for b in blobs)
+        blobs = self._exchange((cached, buf.raw if rc == 0 else None))
+        if all(c for c, _ in blobs):
+            return self._registered[key]
+        if self._registered.pop(key, False):
+            _lib.check(self._lib.b2c_deregister(self._h, ctypes.c_void_p(key[0])))
+        ok = all(b is not None for _, b in blobs)
         if ok:
-            joined = b"".join(bytes(b) for b in blobs)
+            joined = b"".join(bytes(b) for _, b in blobs)
             _lib.check(self._lib.b2c_register_import(self._h, ctypes.c_void_p(key[0]), key[1], joined,
                                                      _lib.REG_BLOB_BYTES))
         self._registered[key] = ok
@@ -203,10 +255,92 @@ class Comm(_Base):
             self._nvls_base, self._nvls_bytes, self._nvls_top = base.value, nbytes.value, 0
         return self._nvls
 
+    def autotune(self, sizes=(32 << 10, 128 << 10, 512 << 10, 2 << 20), iters=7, force=False):
+        """Collective, once per comm: measure where each allreduce path starts to win at THIS world size on THIS
+        box and set the AUTO thresholds from it (the crossover is measured, not assumed).
+        Paths timed per size (fp32, CUDA events, median, max over ranks): staged one-shot, zero-copy two-shot on
+        a registered buffer, in-switch (NVLS) in place when the multicast arena is up.  Rank 0's table decides
+        for everyone (thresholds must be identical on all ranks).  B2C_AUTOTUNE=0 keeps the built-in defaults;
+        explicit B2C_* threshold variables still win afterwards.  Returns the table (also kept in .tuning)."""
+        if self.world == 1 or (getattr(self, "tuning", None) is not None and not force):
+            return getattr(self, "tuning", None)
+        if os.environ.get("B2C_AUTOTUNE", "1") == "0":
+            self.tuning = {"skipped": "B2C_AUTOTUNE=0"}
+            return self.tuning
+        dev = torch.device("cuda", self.device)
+        rows = []
+        with torch.cuda.device(dev):
+            for S in sizes:
+                n = S // 4
+                x = torch.ones(n, device=dev)
+                reg = self.register(x)
+                y = None
+                if self._nvls:
+                    try:
+                        y = self.nvls_empty(n).fill_(1.0)
+                    except MemoryError:
+                        y = None
+                cands = [("oneshot", x, ALGO_ONESHOT)]
+                if reg:
+                    cands.append(("zerocopy", x, ALGO_TWOSHOT))
+                if y is not None:
+                    cands.append(("nvls", y, ALGO_NVLS))
+                row = {"bytes": S}
+                for name, t, algo in cands:
+                    for _ in range(3):
+                        self.allreduce(t, scale=1.0 / self.world, algo=algo)
+                    ts = []
+                    for _ in range(iters):
+                        self.barrier()
+                        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        a.record()
+                        self.allreduce(t, scale=1.0 / self.world, algo=algo)
+                        b.record()
+                        b.synchronize()
+                        ts.append(a.elapsed_time(b) * 1e3)
+                    ts.sort()
+                    row[name] = ts[len(ts) // 2]
+                if y is not None:
+                    self.nvls_free(y)
+                if reg:
+                    self.deregister(x)
+                rows.append(row)
+        allrows = self._exchange(rows)
+        merged = []
+        for i, S in enumerate(sizes):   # per size and path: the slowest rank's median
+            m = {"bytes": S}
+            for k in ("oneshot", "zerocopy", "nvls"):
+                vals = [r[i][k] for r in allrows if k in r[i]]
+                if len(vals) == self.world:
+                    m[k] = max(vals)
+            merged.append(m)
+
+        def first_win(path, margin=0.97):
+            """Smallest measured size from which `path` beats the staged one-shot at every larger measured size."""
+            thr = None
+            for m in reversed(merged):
+                if path in m and m[path] <= margin * m["oneshot"]:
+                    thr = m["bytes"]
+                else:
+                    break
+            return thr
+
+        big = 1 << 40
+        zc, nv = first_win("zerocopy"), first_win("nvls")
+        decided = {"zerocopy_min_bytes": zc if zc is not None else (sizes[-1] * 2 if any("zerocopy" in m for m in merged) else big),
+                   "nvls_min_bytes": nv if nv is not None else (sizes[-1] * 2 if any("nvls" in m for m in merged) else 0)}
+        decided = self._exchange(decided)[0]          # rank 0 decides
+        self.set_param(_lib.PARAM_ZEROCOPY_MIN_BYTES, decided["zerocopy_min_bytes"])
+        if decided["nvls_min_bytes"]:
+            self.set_param(_lib.PARAM_NVLS_MIN_BYTES, decided["nvls_min_bytes"])
+        self._apply_env()                              # explicit environment settings keep the last word
+        self.tuning = {"world": self.world, "table_us": merged, **decided}
+        return self.tuning
+
     def nvls_empty(self, numel, dtype=torch.float32):
-        """A tensor INSIDE the multicast arena (bump allocation, 256-byte aligned, never freed):
-        allreduce on it runs in place in the switch with no staging.  Every rank must allocate
-        the same sequence of sizes so that offsets match."""
+        """A tensor INSIDE the multicast arena (first-fit allocation, 256-byte aligned; give it back with
+        nvls_free): allreduce on it runs in place in the switch with no staging.  Every rank must issue
+        the same sequence of allocations and frees so that offsets match."""
         if not self._nvls:
             raise RuntimeError("multicast arena is not set up (enable_nvls)")
         es = torch.empty(0, dtype=dtype).element_size()
@@ -225,6 +359,11 @@ class Comm(_Base):
                                         "strides": None}
         flat = torch.as_tensor(raw, device=torch.device("cuda", self.device))
         return flat[:numel * es].view(dtype)
+
+    def nvls_free(self, t):
+        """Return a tensor obtained from nvls_empty to the arena (same order on every rank)."""
+        if self._nvls and getattr(self, "_h", None):
+            _lib.check(self._lib.b2c_nvls_free(self._h, ctypes.c_void_p(t.data_ptr())))
 
     def torch_pool(self):
         """A torch.cuda.MemPool whose segments come out of the multicast arena: tensors allocated
@@ -246,9 +385,12 @@ class Comm(_Base):
         return self._nvls
 
     def deregister(self, t):
-        key = (t.data_ptr(), t.numel() * t.element_size())
-        if self._registered.pop(key, False):
-            _lib.check(self._lib.b2c_deregister(self._h, ctypes.c_void_p(key[0])))
+        self.deregister_ptr(t.data_ptr(), t.numel() * t.element_size())
+
+    def deregister_ptr(self, ptr, nbytes):
+        """Local: forget a registration (the memory is about to be freed or was replaced)."""
+        if self._registered.pop((ptr, nbytes), False):
+            _lib.check(self._lib.b2c_deregister(self._h, ctypes.c_void_p(ptr)))
 
     def allreduce(self, t, scale=None, wire_dtype=None, algo=ALGO_AUTO, stream=None):
         """In place: t = sum_r t_r * scale (default 1/world), fp32 accumulate in rank order."""
@@ -265,6 +407,27 @@ class Comm(_Base):
         _lib.check(self._lib.b2c_broadcast(self._h, ctypes.c_void_p(t.data_ptr()), t.numel() * t.element_size(),
                                            int(root), _stream_ptr(stream)))
         return t
+
+    def fused_shard(self, count):
+        """(first element, number of elements) of the shard of a `count`-element bucket this rank owns in
+        fused_step: the optimizer state buffers cover exactly that range."""
+        return fused_shard(self._lib, count, self.world, self.rank)
+
+    def fused_step(self, grad, param, opt, state1, state2, scale=None, bcast=None, bcast_root=0, stream=None):
+        """Gradient average + optimizer update in one launch (b2c_fused_step): `param` (same layout as `grad`) is
+        updated on every rank from the averaged `grad`; `opt` is a _lib.Opt; state1/2 are this rank's fp32 shard
+        state tensors (or None).  `bcast`: optional uint8 tensor inside the multicast arena replicated from
+        `bcast_root` in the same launch."""
+        _check_tensor(grad)
+        _check_tensor(param)
+        if scale is None:
+            scale = 1.0 / self.world
+        bp, bn = (ctypes.c_void_p(bcast.data_ptr()), bcast.numel() * bcast.element_size()) if bcast is not None else (None, 0)
+        _lib.check(self._lib.b2c_fused_step(self._h, ctypes.c_void_p(grad.data_ptr()), ctypes.c_void_p(param.data_ptr()),
+                                            grad.numel(), _DTYPES[grad.dtype], ctypes.c_float(scale), ctypes.byref(opt),
+                                            ctypes.c_void_p(state1.data_ptr()) if state1 is not None else None,
+                                            ctypes.c_void_p(state2.data_ptr()) if state2 is not None else None,
+                                            bp, bn, int(bcast_root), _stream_ptr(stream)))
 
     def barrier(self, stream=None):
         _lib.check(self._lib.b2c_barrier(self._h, _stream_ptr(stream)))
@@ -322,6 +485,19 @@ class LocalGroup(_Base):
         _lib.check(self._lib.b2c_group_broadcast(self._arr, self._ptrs(tensors), nbytes, int(root),
                                                  _stream_ptr(stream)))
         return tensors
+
+    def fused_step(self, grads, params, opt, state1, state2, scale=None, stream=None):
+        """b2c_group_fused_step: per virtual rank gradient / parameter buckets and shard state tensors."""
+        if scale is None:
+            scale = 1.0 / self.world
+        n = grads[0].numel()
+
+        def arr(ts):
+            return (ctypes.c_void_p * self.world)(*[(t.data_ptr() if t is not None else None) for t in ts])
+
+        _lib.check(self._lib.b2c_group_fused_step(self._arr, self._ptrs(grads), self._ptrs(params), n, _DTYPES[grads[0].dtype],
+                                                  ctypes.c_float(scale), ctypes.byref(opt), arr(state1), arr(state2),
+                                                  _stream_ptr(stream)))
 
     def barrier(self, stream=None):
         _lib.check(self._lib.b2c_group_barrier(self._arr, _stream_ptr(stream)))

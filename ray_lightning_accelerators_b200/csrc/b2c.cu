@@ -8,6 +8,7 @@
 #include <sys/syscall.h>
 #include <errno.h>
 #include <pthread.h>
+#include <math.h>
 #include <cuda.h>   // types only: the driver API is reached through cudaGetDriverEntryPoint (no -lcuda)
 
 #include "b2c_kernels.cuh"
@@ -85,14 +86,20 @@ struct b2c_comm {
   struct Nvls* nvls;                 // multicast arena (optional)
 };
 
+#define B2C_NVLS_MAX_BLOCKS 512
+struct ArenaBlock { size_t off, size; bool used; };
 struct Nvls {
   int phase;                              // 1 exported, 2 imported, 3 bound (usable)
-  size_t bytes, slot_bytes;
+  size_t bytes;
+  size_t slot_bytes, slot_off;            // staging slots (2 x slot_bytes at slot_off), carved out on first use
   CUmemGenericAllocationHandle mem, mc;
   int mc_fd;                              // rank 0: exported fd of the multicast object
   CUdeviceptr uc, mcva;
   bool uc_mapped, mc_mapped, bound;
-  size_t top, last;                       // bump allocator inside the arena
+  // first-fit allocator with coalescing over [B2C_MC_HEAD_BYTES, bytes): address ordered block list.
+  // Deterministic: ranks that issue the same alloc/free sequence get the same offsets.
+  ArenaBlock blocks[B2C_NVLS_MAX_BLOCKS];
+  int nblocks;
 };
 struct Registration {
   char* local;                       // caller pointer on this rank
@@ -118,6 +125,7 @@ struct RegBlob {
 static_assert(sizeof(RegBlob) <= B2C_REG_BLOB_BYTES, "reg blob too large");
 
 static void nvls_release(b2c_comm* c);
+static int nvls_stage_slots(b2c_comm* c);
 static pthread_mutex_t g_pool_lock = PTHREAD_MUTEX_INITIALIZER;
 static b2c_comm* g_pool_comm = nullptr;  // whose multicast arena backs b2c_pool_alloc / b2c_pool_free
 
@@ -147,6 +155,12 @@ static void default_params(b2c_comm* c) {
   c->params[B2C_PARAM_MAX_BLOCKS_NVLS] = 8;   // the switch saturates with 4-8 CTAs; more only adds congestion
   c->params[B2C_PARAM_UNROLL_NVLS] = 8;
   c->params[B2C_PARAM_UNROLL_ZC] = 0;
+  c->params[B2C_PARAM_PDL] = 1;
+  c->params[B2C_PARAM_THREADS_NVLS] = 512;
+  c->params[B2C_PARAM_NVLS_LEAN] = 1;
+  c->params[B2C_PARAM_BCAST_MC] = 1;
+  c->params[B2C_PARAM_MC_ACQ_POLL] = 1;
+  c->params[B2C_PARAM_NVLS_STAGE_BYTES] = 32l << 20;
 }
 
 static int comm_alloc(int rank, int world, int device, size_t arena_bytes, b2c_comm** out) {
@@ -368,6 +382,17 @@ static const void* nvls_fn(int mode, int unroll) {
     default: return (const void*)k_allreduce_nvls<MODE_BF16, 8>;
   }
 }
+// lean in-place NVLS kernel: (threads, vectors in flight per thread).  256-thread variants are built for
+// <= 64 registers so that a CTA fits on an SM beside the backward kernels of a training step.
+static const void* nvls_lean_fn(int mode, int threads, int unroll) {
+  if (mode == MODE_F32) {
+    if (threads <= 256) return unroll <= 4 ? (const void*)k_nvls_inplace<MODE_F32, 4, 256, 4> : (const void*)k_nvls_inplace<MODE_F32, 8, 256, 4>;
+    return unroll <= 4 ? (const void*)k_nvls_inplace<MODE_F32, 4, 512, 1> : (const void*)k_nvls_inplace<MODE_F32, 8, 512, 1>;
+  }
+  if (threads <= 256) return unroll <= 4 ? (const void*)k_nvls_inplace<MODE_BF16, 4, 256, 4> : (const void*)k_nvls_inplace<MODE_BF16, 8, 256, 4>;
+  return unroll <= 4 ? (const void*)k_nvls_inplace<MODE_BF16, 4, 512, 1> : (const void*)k_nvls_inplace<MODE_BF16, 8, 512, 1>;
+}
+
 static const void* zc8_fn(int mode, int unroll) {
   if (mode == MODE_F32) {
     switch (unroll) {
@@ -384,9 +409,13 @@ static const void* zc8_fn(int mode, int unroll) {
 }
 
 // registration covering [p, p+bytes), or NULL
+// An exact (pointer, size) match wins; otherwise the NEWEST registration that contains the range (an older
+// one may describe memory that has since been freed and handed out again).
 static Registration* find_reg(b2c_comm* c, const void* p, size_t bytes) {
   const char* q = (const char*)p;
-  for (int i = 0; i < c->nregs; ++i)
+  for (int i = c->nregs - 1; i >= 0; --i)
+    if (q == c->regs[i].local && bytes == c->regs[i].bytes) return &c->regs[i];
+  for (int i = c->nregs - 1; i >= 0; --i)
     if (q >= c->regs[i].local && q + bytes <= c->regs[i].local + c->regs[i].bytes) return &c->regs[i];
   return nullptr;
 }
@@ -475,6 +504,28 @@ static int do_launch(b2c_comm* lead, Launch& L, int grid_y, cudaStream_t stream)
   return B2C_OK;
 }
 
+// Launch with programmatic stream serialization: the grid may become resident while the previous kernel
+// on the stream is still draining (it waits in griddepcontrol.wait); only for kernels that execute that wait.
+static int launch_pdl(b2c_comm* c, const void* fn, void* args, int nblocks, int threads, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(nblocks);
+  cfg.blockDim = dim3(threads);
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = c->params[B2C_PARAM_PDL] ? 1 : 0;
+  void* params[] = {args};
+  cudaError_t e = cudaLaunchKernelExC(&cfg, fn, params);
+  if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, "kernel launch"); }
+  c->stats.launches++;
+  c->stats.last_blocks = nblocks;
+  c->stats.last_threads = threads;
+  return B2C_OK;
+}
+
 static void fill_common(b2c_comm* c, B2cKArgs& a, bool group) {
   memset(&a, 0, sizeof(a));
   for (int q = 0; q < c->world; ++q) a.region[q] = c->peer_region[q];
@@ -543,26 +594,58 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
     // the staged one-shot kernel as a second, tiny launch.
     const size_t tail = inside ? count % (size_t)vw : 0;
     const size_t body = count - tail;
-    const size_t piece = inside ? (body ? body : 1) : (nv->slot_bytes / 16) * vw;
-    for (size_t off = 0; off < body; off += piece) {
-      const size_t n = (body - off < piece) ? body - off : piece;
-      Launch L;
-      fill_common(c, L.args, false);
-      L.args.buf[c->rank] = p + off * ub;
-      L.args.count = n;
-      L.args.scale = scale;
-      L.args.nvls_uc = (char*)nv->uc;
-      L.args.nvls_mc = (char*)nv->mcva;
-      L.args.nvls_slot_bytes = nv->slot_bytes;
-      L.args.nvls_inplace = inside ? 1 : 0;
-      L.args.nvls_off = inside ? (size_t)(p - (char*)nv->uc) : 0;
-      const size_t nvec = (n + vw - 1) / vw;
-      L.fn = nvls_fn(mode, (int)c->params[B2C_PARAM_UNROLL_NVLS]);
-      geometry(c, (nvec + W - 1) / W, c->params[B2C_PARAM_MAX_BLOCKS_NVLS], &L.nblocks, &L.threads, &L.args.chunk_vecs);
+    if (inside && body && c->params[B2C_PARAM_NVLS_LEAN]) {
+      // the hot path of a training step: one lean launch, multicast flag barrier, no staging
+      B2cNvlsArgs a;
+      memset(&a, 0, sizeof(a));
+      a.uc = (char*)nv->uc; a.mc = (char*)nv->mcva;
+      a.ctl = (uint32_t*)c->region; a.status = c->status_d;
+      a.off = (size_t)(p - (char*)nv->uc);
+      a.nvec = body / vw;
+      a.timeout_ns = (unsigned long long)c->params[B2C_PARAM_TIMEOUT_MS] * 1000000ull;
+      a.scale = scale; a.rank = c->rank; a.world = W;
+      a.acq_poll = (int)c->params[B2C_PARAM_MC_ACQ_POLL];
+      const int threads = c->params[B2C_PARAM_THREADS_NVLS] <= 256 ? 256 : 512;
+      const int unroll = c->params[B2C_PARAM_UNROLL_NVLS] <= 4 ? 4 : 8;
+      const size_t nvs = (a.nvec + W - 1) / W;
+      const size_t per = (size_t)threads * unroll;                 // vectors one CTA moves per iteration
+      long mb = c->params[B2C_PARAM_MAX_BLOCKS_NVLS];
+      if (threads <= 256) mb *= 2;                                 // same bytes in flight with half-size CTAs
+      if (mb > B2C_MAX_BLOCKS) mb = B2C_MAX_BLOCKS;
+      size_t nb = (nvs + per - 1) / per;
+      if (nb < 1) nb = 1;
+      if (nb > (size_t)mb) nb = mb;
+      a.chunk_vecs = (uint32_t)per;
       c->stats.nvls_launches++;
       c->stats.last_algo = B2C_ALGO_NVLS;
-      rc = do_launch(c, L, 1, stream);
+      rc = launch_pdl(c, nvls_lean_fn(mode, threads, unroll), &a, (int)nb, threads, stream);
       if (rc) return rc;
+    } else {
+      if (!inside) {
+        rc = nvls_stage_slots(c);
+        if (rc) return rc;
+      }
+      const size_t piece = inside ? (body ? body : 1) : (nv->slot_bytes / 16) * vw;
+      for (size_t off = 0; off < body; off += piece) {
+        const size_t n = (body - off < piece) ? body - off : piece;
+        Launch L;
+        fill_common(c, L.args, false);
+        L.args.buf[c->rank] = p + off * ub;
+        L.args.count = n;
+        L.args.scale = scale;
+        L.args.nvls_uc = (char*)nv->uc;
+        L.args.nvls_mc = (char*)nv->mcva;
+        L.args.nvls_slot_bytes = nv->slot_bytes;
+        L.args.nvls_inplace = inside ? 1 : 0;
+        L.args.nvls_off = inside ? (size_t)(p - (char*)nv->uc) : nv->slot_off;
+        const size_t nvec = (n + vw - 1) / vw;
+        L.fn = nvls_fn(mode, (int)c->params[B2C_PARAM_UNROLL_NVLS]);
+        geometry(c, (nvec + W - 1) / W, c->params[B2C_PARAM_MAX_BLOCKS_NVLS], &L.nblocks, &L.threads, &L.args.chunk_vecs);
+        c->stats.nvls_launches++;
+        c->stats.last_algo = B2C_ALGO_NVLS;
+        rc = do_launch(c, L, 1, stream);
+        if (rc) return rc;
+      }
     }
     if (tail) {
       void* tb[B2C_MAX_WORLD] = {0};
@@ -610,6 +693,13 @@ static int allreduce_impl(b2c_comm* c, void* const* bufs, bool group, size_t cou
     }
   }
 
+  // ---- a single rank averaging over itself: the result is the input, bit for bit (x * 1.0f == x, NaN
+  // payloads included); a bf16 wire would still round, so that mode goes on
+  if (W == 1 && scale == 1.0f && mode != MODE_F32_BF16) {
+    c->stats.last_algo = B2C_ALGO_ONESHOT;
+    c->stats.noop_calls++;
+    return B2C_OK;
+  }
   // ---- a single rank: streaming scale pass, no arena, no flags
   if (W == 1 && mode != MODE_F32_BF16 && (((uintptr_t)bufs[c->rank < 0 ? 0 : c->rank]) & 15u) == 0) {
     void* b = bufs[c->rank];
@@ -681,6 +771,38 @@ static int broadcast_impl(b2c_comm* c, void* const* bufs, bool group, size_t byt
   for (int r = 0; r < c->world; ++r)
     if ((group || r == c->rank) && !bufs[r]) return fail(B2C_EINVAL, "b2c_broadcast: buf is NULL");
   DeviceGuard g(c->device);
+  // ---- through the switch: root sends S once (multimem.st), everyone else copies locally
+  const bool nvls_up = !group && c->nvls && c->nvls->phase == 3;
+  if (nvls_up && c->params[B2C_PARAM_BCAST_MC]) {
+    Nvls* nv = c->nvls;
+    char* p = (char*)bufs[c->rank];
+    // in place: the tensor itself lives in the arena (same offset on every rank), whole vectors only
+    const bool inside = p >= (char*)nv->uc && p + bytes <= (char*)nv->uc + nv->bytes && (((uintptr_t)p & 15u) == 0) && bytes % 16 == 0;
+    if (!inside) {
+      rc = nvls_stage_slots(c);
+      if (rc) return rc;
+    }
+    const size_t piece = inside ? bytes : nv->slot_bytes;
+    for (size_t off = 0; off < bytes; off += piece) {
+      const size_t n = (bytes - off < piece) ? bytes - off : piece;
+      Launch L;
+      fill_common(c, L.args, false);
+      L.args.buf[c->rank] = p + off;
+      L.args.count = n;
+      L.args.root = root;
+      L.args.nvls_uc = (char*)nv->uc;
+      L.args.nvls_mc = (char*)nv->mcva;
+      L.args.nvls_slot_bytes = nv->slot_bytes;
+      L.args.nvls_inplace = inside ? 1 : 0;
+      L.args.nvls_off = inside ? (size_t)(p - (char*)nv->uc) : nv->slot_off;
+      L.fn = (const void*)k_broadcast_mc;
+      geometry(c, (n + 15) / 16, c->params[B2C_PARAM_MAX_BLOCKS_BCAST], &L.nblocks, &L.threads, &L.args.chunk_vecs);
+      c->stats.bcast_mc_launches++;
+      rc = do_launch(c, L, 1, stream);
+      if (rc) return rc;
+    }
+    return B2C_OK;
+  }
   const size_t piece = c->slot_bytes;
   for (size_t off = 0; off < bytes; off += piece) {
     const size_t n = (bytes - off < piece) ? bytes - off : piece;
@@ -875,7 +997,6 @@ extern "C" int b2c_nvls_export(b2c_comm* c, size_t bytes, void* blob, size_t* le
   size_t size = (bytes + gran - 1) / gran * gran;
   Nvls* n = (Nvls*)calloc(1, sizeof(Nvls));
   n->bytes = size;
-  n->slot_bytes = (size / 2) & ~(size_t)255;
   n->mc_fd = -1;
   c->nvls = n;
   CUresult r = d->MemCreate(&n->mem, size, &ap, 0);
@@ -959,6 +1080,11 @@ extern "C" int b2c_nvls_bind(b2c_comm* c) {
   DRV(d->MemSetAccess(n->mcva, n->bytes, &acc, 1), "cuMemSetAccess(mc)");
   CU(cudaMemset((void*)n->uc, 0, n->bytes));
   CU(cudaDeviceSynchronize());
+  if (n->bytes <= B2C_MC_HEAD_BYTES + 4096) return fail(B2C_EINVAL, "b2c_nvls_bind: arena of %zu bytes is too small", n->bytes);
+  n->blocks[0].off = B2C_MC_HEAD_BYTES;   // [0, head): multicast flag counters
+  n->blocks[0].size = n->bytes - B2C_MC_HEAD_BYTES;
+  n->blocks[0].used = false;
+  n->nblocks = 1;
   n->phase = 3;
   return B2C_OK;
 }
@@ -971,22 +1097,87 @@ extern "C" int b2c_nvls_arena(b2c_comm* c, void** base, size_t* bytes) {
   return B2C_OK;
 }
 
+// first fit over the address-ordered block list; caller holds g_pool_lock
+static int arena_alloc_locked(Nvls* n, size_t bytes, size_t* off) {
+  const size_t need = ((bytes ? bytes : 1) + 255) & ~(size_t)255;
+  for (int i = 0; i < n->nblocks; ++i) {
+    ArenaBlock& b = n->blocks[i];
+    if (b.used || b.size < need) continue;
+    if (b.size > need) {
+      if (n->nblocks == B2C_NVLS_MAX_BLOCKS) return fail(B2C_ETOOBIG, "b2c_nvls_alloc: more than %d live blocks", B2C_NVLS_MAX_BLOCKS);
+      memmove(&n->blocks[i + 2], &n->blocks[i + 1], (size_t)(n->nblocks - i - 1) * sizeof(ArenaBlock));
+      n->blocks[i + 1].off = b.off + need;
+      n->blocks[i + 1].size = b.size - need;
+      n->blocks[i + 1].used = false;
+      n->nblocks++;
+      n->blocks[i].size = need;
+    }
+    n->blocks[i].used = true;
+    *off = n->blocks[i].off;
+    return B2C_OK;
+  }
+  size_t used = 0;
+  for (int i = 0; i < n->nblocks; ++i) if (n->blocks[i].used) used += n->blocks[i].size;
+  return fail(B2C_ETOOBIG, "b2c_nvls_alloc: %zu bytes do not fit (arena %zu, in use %zu, %d blocks)", bytes, n->bytes, used, n->nblocks);
+}
+static int arena_free_locked(Nvls* n, size_t off) {
+  for (int i = 0; i < n->nblocks; ++i) {
+    if (n->blocks[i].off != off || !n->blocks[i].used) continue;
+    n->blocks[i].used = false;
+    if (i + 1 < n->nblocks && !n->blocks[i + 1].used) {  // merge with the right neighbour
+      n->blocks[i].size += n->blocks[i + 1].size;
+      memmove(&n->blocks[i + 1], &n->blocks[i + 2], (size_t)(n->nblocks - i - 2) * sizeof(ArenaBlock));
+      n->nblocks--;
+    }
+    if (i > 0 && !n->blocks[i - 1].used) {               // and with the left one
+      n->blocks[i - 1].size += n->blocks[i].size;
+      memmove(&n->blocks[i], &n->blocks[i + 1], (size_t)(n->nblocks - i - 1) * sizeof(ArenaBlock));
+      n->nblocks--;
+    }
+    return B2C_OK;
+  }
+  return fail(B2C_EINVAL, "b2c_nvls_free: offset %zu is not a live allocation", off);
+}
+
 extern "C" int b2c_nvls_alloc(b2c_comm* c, size_t bytes, void** ptr) {
   if (!c || !ptr) return fail(B2C_EINVAL, "b2c_nvls_alloc: NULL argument");
   if (!c->nvls || c->nvls->phase != 3) return fail(B2C_ESTATE, "b2c_nvls_alloc: multicast arena is not set up");
   Nvls* n = c->nvls;
-  const size_t need = (bytes + 255) & ~(size_t)255;
+  size_t off = 0;
   pthread_mutex_lock(&g_pool_lock);
-  int rc = B2C_OK;
-  if (n->top + need > n->bytes) {
-    rc = fail(B2C_ETOOBIG, "b2c_nvls_alloc: %zu bytes do not fit (arena %zu, used %zu)", bytes, n->bytes, n->top);
-  } else {
-    n->last = n->top;
-    *ptr = (void*)(n->uc + n->top);
-    n->top += need;
-  }
+  int rc = arena_alloc_locked(n, bytes, &off);
+  pthread_mutex_unlock(&g_pool_lock);
+  if (rc == B2C_OK) *ptr = (void*)(n->uc + off);
+  return rc;
+}
+extern "C" int b2c_nvls_free(b2c_comm* c, void* ptr) {
+  if (!c) return fail(B2C_EINVAL, "b2c_nvls_free: comm is NULL");
+  if (!c->nvls || c->nvls->phase != 3) return fail(B2C_ESTATE, "b2c_nvls_free: multicast arena is not set up");
+  Nvls* n = c->nvls;
+  if ((char*)ptr < (char*)n->uc || (char*)ptr >= (char*)n->uc + n->bytes) return fail(B2C_EINVAL, "b2c_nvls_free: %p is outside the arena", ptr);
+  pthread_mutex_lock(&g_pool_lock);
+  int rc = arena_free_locked(n, (size_t)((char*)ptr - (char*)n->uc));
   pthread_mutex_unlock(&g_pool_lock);
   return rc;
+}
+// staging slots for tensors that live OUTSIDE the arena (explicit B2C_ALGO_NVLS requests, the multicast
+// broadcast): 2 x slot, carved out once; collective by construction (every rank makes the same first call)
+static int nvls_stage_slots(b2c_comm* c) {
+  Nvls* n = c->nvls;
+  if (n->slot_bytes) return B2C_OK;
+  size_t slot = (size_t)c->params[B2C_PARAM_NVLS_STAGE_BYTES] & ~(size_t)255;
+  size_t off = 0;
+  int rc = B2C_ETOOBIG;
+  pthread_mutex_lock(&g_pool_lock);
+  for (; slot >= (64u << 10); slot /= 2) {   // same arena state on every rank => same slot size is found
+    rc = arena_alloc_locked(n, 2 * slot, &off);
+    if (rc == B2C_OK) break;
+  }
+  pthread_mutex_unlock(&g_pool_lock);
+  if (rc != B2C_OK) return fail(B2C_ETOOBIG, "b2c: no room left in the multicast arena for staging slots (enlarge B2C_NVLS_ARENA_BYTES)");
+  n->slot_bytes = slot;
+  n->slot_off = off;
+  return B2C_OK;
 }
 extern "C" int b2c_nvls_pool_bind(b2c_comm* c) {
   if (c && (!c->nvls || c->nvls->phase != 3)) return fail(B2C_ESTATE, "b2c_nvls_pool_bind: multicast arena is not set up");
@@ -1003,12 +1194,211 @@ extern "C" void* b2c_pool_alloc(ptrdiff_t size, int device, b2c_stream_t stream)
 }
 extern "C" void b2c_pool_free(void* ptr, ptrdiff_t size, int device, b2c_stream_t stream) {
   (void)size; (void)device; (void)stream;
-  pthread_mutex_lock(&g_pool_lock);
-  if (g_pool_comm && g_pool_comm->nvls) {
-    Nvls* n = g_pool_comm->nvls;
-    if ((char*)ptr == (char*)n->uc + n->last) n->top = n->last;  // LIFO roll-back; anything else stays reserved
+  b2c_comm* c = g_pool_comm;
+  if (c && c->nvls) b2c_nvls_free(c, ptr);  // after the comm is gone the arena is unmapped as a whole
+}
+
+
+// ---------------------------------------------------------------- fused optimizer step (§8(f)4)
+static int opt_to_k(const b2c_opt* o, B2cOptK* k) {
+  if (!o) return fail(B2C_EINVAL, "b2c_fused_step: opt is NULL");
+  if (o->kind != B2C_OPT_SGD && o->kind != B2C_OPT_ADAM && o->kind != B2C_OPT_ADAMW)
+    return fail(B2C_EUNSUPPORTED, "b2c_fused_step: optimizer kind %d (1 = SGD, 2 = Adam, 3 = AdamW)", o->kind);
+  memset(k, 0, sizeof(*k));
+  k->kind = o->kind; k->nesterov = o->nesterov; k->first = o->first_step;
+  k->lr = (float)o->lr; k->momentum = (float)o->momentum; k->one_m_dampening = (float)(1.0 - o->dampening);
+  k->weight_decay = (float)o->weight_decay;
+  k->one_m_beta1 = (float)(1.0 - o->beta1); k->beta2 = (float)o->beta2; k->one_m_beta2 = (float)(1.0 - o->beta2);
+  k->eps = (float)o->eps; k->adamw_keep = (float)(1.0 - o->lr * o->weight_decay);
+  if (o->kind != B2C_OPT_SGD) {
+    if (!(o->bias_correction1 > 0.0) || !(o->bias_correction2 > 0.0))
+      return fail(B2C_EINVAL, "b2c_fused_step: Adam needs bias_correction1/2 = 1 - beta^t > 0");
+    k->step_size = (float)(o->lr / o->bias_correction1);
+    k->bc2_sqrt = (float)sqrt(o->bias_correction2);
   }
-  pthread_mutex_unlock(&g_pool_lock);
+  return B2C_OK;
+}
+
+extern "C" int b2c_fused_shard(size_t count, int world, int rank, size_t* first_elem, size_t* n_elems) {
+  if (world < 1 || world > B2C_MAX_WORLD || rank < 0 || rank >= world) return fail(B2C_EINVAL, "b2c_fused_shard: rank %d of %d", rank, world);
+  if (world == 1) {
+    if (first_elem) *first_elem = 0;
+    if (n_elems) *n_elems = count;
+    return B2C_OK;
+  }
+  const size_t nvec = count / 4, nvs = (nvec + world - 1) / world;
+  const size_t s0 = (size_t)rank * nvs;
+  const size_t sl = s0 >= nvec ? 0 : (s0 + nvs <= nvec ? nvs : nvec - s0);
+  if (first_elem) *first_elem = s0 * 4;
+  if (n_elems) *n_elems = sl * 4;
+  return B2C_OK;
+}
+
+template <int W> static const void* fused_zc_fn_w(int kind) {
+  switch (kind) {
+    case B2C_OPT_SGD: return (const void*)k_fused_step_zc<B2C_OPT_SGD, W>;
+    case B2C_OPT_ADAM: return (const void*)k_fused_step_zc<B2C_OPT_ADAM, W>;
+    default: return (const void*)k_fused_step_zc<B2C_OPT_ADAMW, W>;
+  }
+}
+static const void* fused_zc_fn(int kind, int W) {
+  switch (W) {
+    case 2: return fused_zc_fn_w<2>(kind);
+    case 3: return fused_zc_fn_w<3>(kind);
+    case 4: return fused_zc_fn_w<4>(kind);
+    case 5: return fused_zc_fn_w<5>(kind);
+    case 6: return fused_zc_fn_w<6>(kind);
+    case 7: return fused_zc_fn_w<7>(kind);
+    default: return fused_zc_fn_w<8>(kind);
+  }
+}
+
+// grads / params: group ? per-rank pointers : only [c->rank]
+static int fused_impl(b2c_comm* c, void* const* grads, void* const* params, bool group, size_t count, int dtype, float scale,
+                      const b2c_opt* opt, void* const* st1, void* const* st2, void* bcast_buf, size_t bcast_bytes, int bcast_root,
+                      cudaStream_t stream) {
+  if (!c) return fail(B2C_EINVAL, "b2c_fused_step: comm is NULL");
+  if (!c->ready) return fail(B2C_ESTATE, "b2c_fused_step: comm not imported yet");
+  if (dtype != B2C_F32) return fail(B2C_EUNSUPPORTED, "b2c_fused_step: fp32 gradients and parameters only (dtype=%d)", dtype);
+  int rc = check_sticky(c);
+  if (rc) return rc;
+  B2cOptK ok;
+  rc = opt_to_k(opt, &ok);
+  if (rc) return rc;
+  const int W = c->world;
+  const bool need1 = ok.kind != B2C_OPT_SGD || ok.momentum != 0.f, need2 = ok.kind != B2C_OPT_SGD;
+  for (int r = 0; r < W; ++r) {
+    if (!group && r != c->rank) continue;
+    if (!grads[r] || !params[r]) return fail(B2C_EINVAL, "b2c_fused_step: NULL gradient / parameter bucket");
+    if (((uintptr_t)grads[r] | (uintptr_t)params[r]) & (W == 1 ? 3u : 15u))
+      return fail(B2C_EINVAL, "b2c_fused_step: buckets must be 16-byte aligned");
+    if ((need1 && !st1[r]) || (need2 && !st2[r])) return fail(B2C_EINVAL, "b2c_fused_step: optimizer state buffer missing");
+  }
+  if (W > 1 && count % 4) return fail(B2C_EINVAL, "b2c_fused_step: count=%zu must be a multiple of 4 (buckets are padded to 16 bytes)", count);
+  if (bcast_bytes && (bcast_root < 0 || bcast_root >= W)) return fail(B2C_EINVAL, "b2c_fused_step: bcast_root=%d", bcast_root);
+  c->stats.fused_steps++;
+  if (count == 0 && !bcast_bytes) return B2C_OK;
+  DeviceGuard g(c->device);
+
+  if (W == 1) {   // everything is local: one streaming kernel
+    if (count == 0) return B2C_OK;
+    size_t blocks = (count / 4 + 255) / 256;
+    if (blocks < 1) blocks = 1;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    const float* gp = (const float*)grads[c->rank];
+    float* wp = (float*)params[c->rank];
+    float* a1 = (float*)st1[c->rank];
+    float* a2 = (float*)st2[c->rank];
+    if (((uintptr_t)gp | (uintptr_t)wp | (uintptr_t)a1 | (uintptr_t)a2) & 15u) return fail(B2C_EINVAL, "b2c_fused_step: buffers must be 16-byte aligned");
+    switch (ok.kind) {
+      case B2C_OPT_SGD: k_fused_step_local<B2C_OPT_SGD><<<(unsigned)blocks, 256, 0, stream>>>(gp, wp, a1, a2, count, scale, ok); break;
+      case B2C_OPT_ADAM: k_fused_step_local<B2C_OPT_ADAM><<<(unsigned)blocks, 256, 0, stream>>>(gp, wp, a1, a2, count, scale, ok); break;
+      default: k_fused_step_local<B2C_OPT_ADAMW><<<(unsigned)blocks, 256, 0, stream>>>(gp, wp, a1, a2, count, scale, ok); break;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch (fused step, local)");
+    c->stats.launches++;
+    c->stats.last_blocks = (uint32_t)blocks;
+    c->stats.last_threads = 256;
+    return B2C_OK;
+  }
+
+  // ---- through the switch: both buckets (and the buffers to broadcast) live in the multicast arena
+  Nvls* nv = (!group && c->nvls && c->nvls->phase == 3) ? c->nvls : nullptr;
+  auto inside = [&](const void* p, size_t bytes) {
+    return nv && (const char*)p >= (const char*)nv->uc && (const char*)p + bytes <= (const char*)nv->uc + nv->bytes;
+  };
+  if (nv && inside(grads[c->rank], count * 4) && inside(params[c->rank], count * 4) &&
+      (!bcast_bytes || (inside(bcast_buf, bcast_bytes) && bcast_bytes % 16 == 0 && ((uintptr_t)bcast_buf & 15u) == 0))) {
+    B2cNvlsFusedArgs fa;
+    memset(&fa, 0, sizeof(fa));
+    B2cNvlsArgs& a = fa.n;
+    a.uc = (char*)nv->uc; a.mc = (char*)nv->mcva;
+    a.ctl = (uint32_t*)c->region; a.status = c->status_d;
+    a.off = (size_t)((char*)grads[c->rank] - (char*)nv->uc);
+    a.nvec = count / 4;
+    a.timeout_ns = (unsigned long long)c->params[B2C_PARAM_TIMEOUT_MS] * 1000000ull;
+    a.scale = scale; a.rank = c->rank; a.world = W; a.acq_poll = 1;
+    fa.param_off = (size_t)((char*)params[c->rank] - (char*)nv->uc);
+    fa.st1 = (float*)st1[c->rank]; fa.st2 = (float*)st2[c->rank];
+    if (bcast_bytes) {
+      fa.bcast_off = (size_t)((char*)bcast_buf - (char*)nv->uc);
+      fa.bcast_vecs = bcast_bytes / 16;
+      fa.bcast_root = bcast_root;
+    }
+    fa.opt = ok;
+    const int threads = 512, unroll = 4;
+    const size_t nvs = (a.nvec + W - 1) / W;
+    const size_t per = (size_t)threads * unroll;
+    long mb = c->params[B2C_PARAM_MAX_BLOCKS_NVLS] * 2;   // half the vectors in flight per thread of the plain kernel
+    if (mb > B2C_MAX_BLOCKS) mb = B2C_MAX_BLOCKS;
+    size_t nb = (nvs + per - 1) / per;
+    if (nb < 1) nb = 1;
+    if (nb > (size_t)mb) nb = mb;
+    a.chunk_vecs = (uint32_t)per;
+    const void* fn = ok.kind == B2C_OPT_SGD ? (const void*)k_fused_step_nvls<B2C_OPT_SGD, 4>
+                   : ok.kind == B2C_OPT_ADAM ? (const void*)k_fused_step_nvls<B2C_OPT_ADAM, 4>
+                                             : (const void*)k_fused_step_nvls<B2C_OPT_ADAMW, 4>;
+    c->stats.nvls_launches++;
+    c->stats.last_algo = B2C_ALGO_NVLS;
+    return launch_pdl(c, fn, &fa, (int)nb, threads, stream);
+  }
+
+  // ---- peer to peer: registered buckets (or a local group); the C4 fold is not available here
+  if (bcast_bytes) return fail(B2C_ESTATE, "b2c_fused_step: folding the buffer broadcast into the step needs the multicast arena");
+  Registration* rg = group ? nullptr : find_reg(c, grads[c->rank], count * 4);
+  Registration* rp = group ? nullptr : find_reg(c, params[c->rank], count * 4);
+  if (!group && (!rg || !rp))
+    return fail(B2C_ESTATE, "b2c_fused_step: gradient and parameter buckets must live in the multicast arena or be registered "
+                            "with every peer (b2c_register_*); there is no staged form of the fused step");
+  B2cFusedArgs fa;
+  memset(&fa, 0, sizeof(fa));
+  fill_common(c, fa.k, group);
+  for (int r = 0; r < W; ++r) {
+    if (group) {
+      fa.k.buf[r] = grads[r]; fa.pbuf[r] = params[r];
+      fa.st1[r] = (float*)st1[r]; fa.st2[r] = (float*)st2[r];
+    } else {
+      fa.k.buf[r] = rg->peer[r] + ((char*)grads[c->rank] - rg->local);
+      fa.pbuf[r] = rp->peer[r] + ((char*)params[c->rank] - rp->local);
+    }
+  }
+  if (!group) { fa.st1[c->rank] = (float*)st1[c->rank]; fa.st2[c->rank] = (float*)st2[c->rank]; }
+  fa.k.count = count;
+  fa.k.scale = scale;
+  fa.opt = ok;
+  Launch L;
+  L.fn = fused_zc_fn(ok.kind, W);
+  long mb = c->params[B2C_PARAM_MAX_BLOCKS_TWOSHOT];
+  if (group) mb = group_block_cap(c, L.fn, mb);
+  const size_t nvs = (count / 4 + W - 1) / W;
+  geometry(c, nvs, mb, &L.nblocks, &L.threads, &fa.k.chunk_vecs);
+  void* kp[] = {(void*)&fa};
+  dim3 grid(L.nblocks, group ? W : 1), block(L.threads);
+  cudaError_t e = group ? cudaLaunchCooperativeKernel(L.fn, grid, block, kp, 0, stream) : cudaLaunchKernel(L.fn, grid, block, kp, 0, stream);
+  if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, "kernel launch (fused step)"); }
+  c->stats.launches++;
+  c->stats.twoshot_launches++;
+  c->stats.zerocopy_launches++;
+  c->stats.last_algo = B2C_ALGO_TWOSHOT;
+  c->stats.last_blocks = L.nblocks;
+  c->stats.last_threads = L.threads;
+  return B2C_OK;
+}
+
+extern "C" int b2c_fused_step(b2c_comm* c, void* grad, void* param, size_t count, int dtype, float scale, const b2c_opt* opt,
+                              void* state1, void* state2, void* bcast_buf, size_t bcast_bytes, int bcast_root, b2c_stream_t stream) {
+  if (c && c->local_group) return fail(B2C_ESTATE, "b2c_fused_step: comm belongs to a local group; use b2c_group_fused_step");
+  void* g[B2C_MAX_WORLD] = {0}; void* p[B2C_MAX_WORLD] = {0}; void* a1[B2C_MAX_WORLD] = {0}; void* a2[B2C_MAX_WORLD] = {0};
+  if (c && c->rank >= 0 && c->rank < B2C_MAX_WORLD) { g[c->rank] = grad; p[c->rank] = param; a1[c->rank] = state1; a2[c->rank] = state2; }
+  return fused_impl(c, g, p, false, count, dtype, scale, opt, a1, a2, bcast_buf, bcast_bytes, bcast_root, (cudaStream_t)stream);
+}
+extern "C" int b2c_group_fused_step(b2c_comm** comms, void** grads, void** params, size_t count, int dtype, float scale,
+                                    const b2c_opt* opt, void** state1, void** state2, b2c_stream_t stream) {
+  int rc = group_check(comms, "b2c_group_fused_step");
+  if (rc) return rc;
+  if (!grads || !params || !state1 || !state2) return fail(B2C_EINVAL, "b2c_group_fused_step: NULL argument");
+  return fused_impl(comms[0], grads, params, true, count, dtype, scale, opt, state1, state2, nullptr, 0, 0, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------- allocation-free local allreduce
@@ -1018,34 +1408,42 @@ extern "C" void b2c_pool_free(void* ptr, ptrdiff_t size, int device, b2c_stream_
 // the library carries it (B2C_MAX_WORLD x (16 KiB header + 256 KiB slot) = 2,228,224 bytes).
 #define B2C_NOALLOC_REGION_BYTES (B2C_HEADER_BYTES + B2C_NOALLOC_MAX_BYTES)
 static __device__ __align__(256) unsigned char g_noalloc_scratch[B2C_MAX_WORLD * B2C_NOALLOC_REGION_BYTES];
+// sticky error words of the allocation-free entry point (code, epoch, channel, peer).  Kept apart from the
+// scratch above because that is wiped at the start of every call; these survive until read and reset.
+static __device__ uint32_t g_noalloc_status[4];
 
 #define B2C_NOALLOC_MAX_DEVICES 64
 static pthread_mutex_t g_noalloc_lock = PTHREAD_MUTEX_INITIALIZER;
 static char* g_noalloc_addr[B2C_NOALLOC_MAX_DEVICES];   // per device: where the array lives ON that device
+static uint32_t* g_noalloc_status_addr[B2C_NOALLOC_MAX_DEVICES];
 static int g_noalloc_blocks[B2C_NOALLOC_MAX_DEVICES];   // per device: co-resident CTAs of the widest kernel
 
 // Once per device, with that device current.  In host code `g_noalloc_scratch` is only a handle for
 // the runtime, not a device address: the address has to be asked for, per device.
-static int noalloc_setup(int dev, char** base, int* resident) {
+static int noalloc_setup(int dev, char** base, int* resident, uint32_t** status = nullptr) {
   if (dev < 0 || dev >= B2C_NOALLOC_MAX_DEVICES) return fail(B2C_EINVAL, "b2c_allreduce_local_noalloc: device %d out of range", dev);
   pthread_mutex_lock(&g_noalloc_lock);
   int rc = B2C_OK;
   if (!g_noalloc_addr[dev]) {
     void* p = nullptr;
+    void* ps = nullptr;
     cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e == cudaSuccess) e = cudaGetSymbolAddress(&ps, g_noalloc_status);
     int per_sm = 0, sms = 0;
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_allreduce_oneshot<MODE_F32, B2C_MAX_WORLD>, 512, 0);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (e != cudaSuccess || !p) {
+    if (e != cudaSuccess || !p || !ps) {
       cudaGetLastError();
       rc = cuda_fail(e, "b2c_allreduce_local_noalloc: set-up (cudaGetSymbolAddress / occupancy)");
     } else {
       g_noalloc_blocks[dev] = per_sm * sms;
+      g_noalloc_status_addr[dev] = (uint32_t*)ps;
       g_noalloc_addr[dev] = (char*)p;
     }
   }
   *base = g_noalloc_addr[dev];
   *resident = g_noalloc_blocks[dev];
+  if (status) *status = g_noalloc_status_addr[dev];
   pthread_mutex_unlock(&g_noalloc_lock);
   return rc;
 }
@@ -1069,8 +1467,9 @@ extern "C" int b2c_allreduce_local_noalloc(void* const* bufs, int world, size_t 
   int dev = -1;
   CU(cudaGetDevice(&dev));
   char* base = nullptr;
+  uint32_t* status = nullptr;
   int resident = 0;
-  rc = noalloc_setup(dev, &base, &resident);
+  rc = noalloc_setup(dev, &base, &resident, &status);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
 
@@ -1082,7 +1481,7 @@ extern "C" int b2c_allreduce_local_noalloc(void* const* bufs, int world, size_t 
     // call counter, exit ticket, error words and flags all have to start from zero
     CU(cudaMemsetAsync(region, 0, B2C_CTL_BYTES + B2C_FLAG_BYTES, st));
     L.args.region[q] = region;
-    L.args.status[q] = reinterpret_cast<uint32_t*>(region + 1024);  // inside the cleared control page
+    L.args.status[q] = status;  // shared by the virtual ranks, NOT wiped per call: see b2c_noalloc_status
     L.args.buf[q] = bufs[q];
   }
   L.args.count = count;
@@ -1108,6 +1507,28 @@ extern "C" int b2c_allreduce_local_noalloc(void* const* bufs, int world, size_t 
   cudaError_t e = (world > 1) ? cudaLaunchCooperativeKernel(L.fn, grid, block, params, 0, st)
                               : cudaLaunchKernel(L.fn, grid, block, params, 0, st);
   if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, "b2c_allreduce_local_noalloc: kernel launch"); }
+  return B2C_OK;
+}
+
+// A flag-barrier timeout inside b2c_allreduce_local_noalloc cannot be returned by the call that hit it (the
+// call only enqueues).  This reads the sticky words back; it waits for the device, allocates nothing, and
+// with `reset` clears them so the entry point can be used again.
+extern "C" int b2c_noalloc_status(uint32_t out[4], int reset) {
+  int dev = -1;
+  CU(cudaGetDevice(&dev));
+  char* base = nullptr;
+  uint32_t* status = nullptr;
+  int resident = 0;
+  int rc = noalloc_setup(dev, &base, &resident, &status);
+  if (rc) return rc;
+  uint32_t st[4] = {0, 0, 0, 0};
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy(st, status, sizeof(st), cudaMemcpyDeviceToHost));
+  if (out) memcpy(out, st, sizeof(st));
+  if (reset && st[0]) CU(cudaMemset(status, 0, sizeof(st)));
+  if (st[0])
+    return fail(-(int)st[0], "b2c_allreduce_local_noalloc: an earlier call timed out in its flag barrier (epoch %u, channel %u, "
+                "waiting for virtual rank %u); the buffers of that call were left unreduced", st[1], st[2], st[3]);
   return B2C_OK;
 }
 
@@ -1216,7 +1637,8 @@ extern "C" int b2c_deregister(b2c_comm* c, void* ptr) {
   if (!c) return fail(B2C_EINVAL, "b2c_deregister: comm is NULL");
   for (int i = 0; i < c->nregs; ++i)
     if (c->regs[i].local == (char*)ptr) {
-      c->regs[i] = c->regs[--c->nregs];  // peer mappings stay open until destroy (shared per allocation)
+      memmove(&c->regs[i], &c->regs[i + 1], (size_t)(c->nregs - i - 1) * sizeof(Registration));  // keeps age order
+      c->nregs--;                        // peer mappings stay open until destroy (shared per allocation)
       return B2C_OK;
     }
   return fail(B2C_EINVAL, "b2c_deregister: %p is not registered", ptr);
@@ -1249,7 +1671,17 @@ extern "C" int b2c_set_param(b2c_comm* c, int key, long v) {
       if (v != 0 && v != 1 && v != 2 && v != 4) return fail(B2C_EINVAL, "b2c_set_param: zero-copy unroll %ld (0, 1, 2 or 4)", v);
       break;
     case B2C_PARAM_ZEROCOPY:
-      if (v != 0 && v != 1) return fail(B2C_EINVAL, "b2c_set_param: zerocopy=%ld (0 or 1)", v);
+    case B2C_PARAM_PDL:
+    case B2C_PARAM_NVLS_LEAN:
+    case B2C_PARAM_BCAST_MC:
+    case B2C_PARAM_MC_ACQ_POLL:
+      if (v != 0 && v != 1) return fail(B2C_EINVAL, "b2c_set_param: key %d takes 0 or 1, got %ld", key, v);
+      break;
+    case B2C_PARAM_THREADS_NVLS:
+      if (v != 256 && v != 512) return fail(B2C_EINVAL, "b2c_set_param: nvls threads %ld (256 or 512)", v);
+      break;
+    case B2C_PARAM_NVLS_STAGE_BYTES:
+      if (v < (64 << 10)) return fail(B2C_EINVAL, "b2c_set_param: staging slot %ld bytes (>= 64 KiB)", v);
       break;
     case B2C_PARAM_ZEROCOPY_MIN_BYTES:
     case B2C_PARAM_NVLS_MIN_BYTES:
@@ -1298,6 +1730,23 @@ extern "C" int b2c_get_phase_ns(b2c_comm* c, uint64_t out[4]) {
   CU(cudaDeviceSynchronize());
   CU(cudaMemcpy(out, c->region + B2C_CTL_PHASE_U64 * 8, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
   return B2C_OK;
+}
+extern "C" int b2c_get_phase_ring(b2c_comm* c, uint64_t* out, int max_entries, uint32_t* total) {
+  if (!c || !out || !total) return fail(B2C_EINVAL, "b2c_get_phase_ring: NULL argument");
+  DeviceGuard g(c->device);
+  CU(cudaDeviceSynchronize());
+  uint32_t seq = 0;
+  CU(cudaMemcpy(&seq, c->region + B2C_CTL_PHASE_SEQ * 4, 4, cudaMemcpyDeviceToHost));
+  uint64_t ring[B2C_PHASE_RING * 4];
+  CU(cudaMemcpy(ring, c->region + B2C_CTL_RING_BYTE, sizeof(ring), cudaMemcpyDeviceToHost));
+  int n = (int)(seq < (uint32_t)B2C_PHASE_RING ? seq : (uint32_t)B2C_PHASE_RING);
+  if (n > max_entries) n = max_entries;
+  for (int i = 0; i < n; ++i) {   // oldest first
+    const uint32_t k = (seq - (uint32_t)n + (uint32_t)i) % B2C_PHASE_RING;
+    memcpy(out + (size_t)i * 4, ring + (size_t)k * 4, 32);
+  }
+  *total = seq;
+  return n;
 }
 extern "C" int b2c_comm_info(b2c_comm* c, int* rank, int* world, int* device) {
   if (!c) return fail(B2C_EINVAL, "b2c_comm_info: comm is NULL");

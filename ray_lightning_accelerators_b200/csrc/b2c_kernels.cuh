@@ -29,8 +29,19 @@
 #define B2C_CTL_EPOCH 0
 #define B2C_CTL_CALLS 1
 #define B2C_CTL_TICKET 2
-#define B2C_CTL_PHASE_U64 8   /* u64 index: start, after barrier A, after barrier B, end (channel 0) */
+#define B2C_CTL_PHASE_SEQ 3   /* kernels that stamped the phase ring so far (channel 0 only) */
+#define B2C_CTL_PHASE_U64 8   /* u64 index: start, after barrier A, after barrier B, end (channel 0) of the LAST kernel */
+#define B2C_CTL_MC_EPOCH 64   /* u32 index: per-channel epoch of the multicast flag counters (256 words) */
+#define B2C_CTL_RING_BYTE 2048 /* byte offset: ring of the last B2C_PHASE_RING kernels' phase stamps (4 x u64 each) */
+#define B2C_PHASE_RING 32
+/* head of the multicast arena: one 128-byte line per channel holding a monotonic arrival counter that
+ * every rank bumps with ONE multimem.red (the switch adds it into all W copies) and spins on locally */
+#define B2C_MC_FLAG_STRIDE 128
+#define B2C_MC_FLAG_BYTES (B2C_MAX_BLOCKS * B2C_MC_FLAG_STRIDE)
+#define B2C_MC_HEAD_BYTES 65536
 
+static_assert(B2C_CTL_MC_EPOCH * 4 + B2C_MAX_BLOCKS * 4 <= B2C_CTL_RING_BYTE && B2C_CTL_RING_BYTE + B2C_PHASE_RING * 32 <= B2C_CTL_BYTES, "control page layout");
+static_assert(B2C_MC_FLAG_BYTES <= B2C_MC_HEAD_BYTES, "multicast flag head too small");
 static_assert(B2C_MAX_BLOCKS * B2C_MAX_WORLD * 4 <= B2C_FLAG_BYTES && B2C_CTL_BYTES + B2C_FLAG_BYTES <= B2C_HEADER_BYTES, "flag page too small");
 
 enum { MODE_F32 = 0, MODE_BF16 = 1, MODE_F32_BF16 = 2, MODE_U8 = 3 };
@@ -52,7 +63,7 @@ struct B2cKArgs {
   char* nvls_uc;                   // local unicast view of the multicast arena
   char* nvls_mc;                   // multicast view (multimem.* only)
   size_t nvls_slot_bytes;          // staged mode: arena is two slots, picked by call parity
-  size_t nvls_off;                 // in-place mode: offset of the caller's tensor inside the arena
+  size_t nvls_off;                 // in-place: offset of the caller's tensor inside the arena; staged: of slot 0
   int nvls_inplace;
 };
 
@@ -264,11 +275,24 @@ __device__ __forceinline__ Ctx prologue(const B2cKArgs& a) {
   return c;
 }
 
+// channel 0, one thread, at the end of a kernel: keep the stamps of the last B2C_PHASE_RING kernels so
+// that a training step can be attributed bucket by bucket afterwards without any host sync in between
+__device__ __forceinline__ void phase_commit(uint32_t* ctl) {
+  unsigned long long* last = reinterpret_cast<unsigned long long*>(ctl) + B2C_CTL_PHASE_U64;
+  const uint32_t seq = ld_volatile_u32(ctl + B2C_CTL_PHASE_SEQ);
+  unsigned long long* slot = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(ctl) + B2C_CTL_RING_BYTE) +
+                             (size_t)(seq % B2C_PHASE_RING) * 4;
+  slot[0] = last[0]; slot[1] = last[1]; slot[2] = last[2]; slot[3] = last[3];
+  ctl[B2C_CTL_PHASE_SEQ] = seq + 1u;
+}
+
 // last CTA out advances the epoch / call counters for the next launch on this stream
 __device__ __forceinline__ void epilogue(const Ctx& c) {
   __syncthreads();
-  if (blockIdx.x == 0 && threadIdx.x == 0)
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
     reinterpret_cast<unsigned long long*>(c.ctl)[B2C_CTL_PHASE_U64 + 3] = globaltimer_ns();
+    phase_commit(c.ctl);
+  }
   if (threadIdx.x == 0) {
     __threadfence();
     unsigned t = atomicAdd(c.ctl + B2C_CTL_TICKET, 1u);
@@ -634,7 +658,7 @@ __global__ void __launch_bounds__(512, 1) k_allreduce_nvls(const __grid_constant
   const size_t nvs = (nvec + W - 1) / W;
   const bool inplace = a.nvls_inplace != 0;
   const bool fast = ((reinterpret_cast<uintptr_t>(buf) & 15u) == 0);
-  const size_t base = inplace ? a.nvls_off : (size_t)(c.calls & 1u) * a.nvls_slot_bytes;
+  const size_t base = inplace ? a.nvls_off : a.nvls_off + (size_t)(c.calls & 1u) * a.nvls_slot_bytes;
   char* uc = a.nvls_uc + base;
   char* mc = a.nvls_mc + base;
 
@@ -680,6 +704,383 @@ __global__ void __launch_bounds__(512, 1) k_allreduce_nvls(const __grid_constant
     }
   }
   epilogue(c);
+}
+
+
+// ================================================================= broadcast through the switch
+// With the multicast arena up the root sends its bytes ONCE: multimem.st replicates every 16-byte vector
+// into all W copies of an arena range (a staging slot picked by call parity, or the tensor's own place
+// when it lives in the arena at the same offset on every rank), one flag barrier, and every other rank
+// copies slot -> buffer locally at HBM rate.  Root egress S instead of (W-1)*S.
+__global__ void __launch_bounds__(512, 1) k_broadcast_mc(const __grid_constant__ B2cKArgs a) {
+  Ctx c = prologue(a);
+  void* buf = a.buf[c.rank];
+  const size_t count = a.count;
+  const size_t nvec = (count + 15) / 16;
+  const bool inplace = a.nvls_inplace != 0;
+  const bool fast = ((reinterpret_cast<uintptr_t>(buf) & 15u) == 0);
+  const size_t base = inplace ? a.nvls_off : a.nvls_off + (size_t)(c.calls & 1u) * a.nvls_slot_bytes;
+  char* mc = a.nvls_mc + base;
+  const char* uc = a.nvls_uc + base;
+  // In place the root writes straight into the peers' tensors, so it has to know that every peer has reached
+  // this call (whatever wrote that memory earlier on the peer's stream is done): entry barrier.  A staging slot
+  // is only ever written by broadcast kernels and is double buffered, so the staged form needs none.
+  if (inplace) channel_barrier(a, c, c.epoch + 1u);
+  if (c.rank == a.root && !c.dead) {
+    B2C_FOR_OWNED(nvec, 8, {
+      uint4 v[8];
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = load_user<MODE_U8>(buf, idx[u], count, fast);
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) multimem_st_v4(mc + idx[u] * 16, v[u]);
+    })
+  }
+  channel_barrier(a, c, c.epoch + (inplace ? 2u : 1u));
+  if (!c.dead && c.rank != a.root && !inplace) {
+    B2C_FOR_OWNED(nvec, 8, {
+      uint4 v[8];
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) v[u] = ld_sys_v4(uc + idx[u] * 16);
+      _Pragma("unroll") for (int u = 0; u < 8; ++u) if (pred[u]) store_user<MODE_U8>(buf, idx[u], count, fast, v[u]);
+    })
+  }
+  epilogue(c);
+}
+
+
+// ================================================================= NVLS in place, lean (the per-step hot kernel)
+// The tensor lives in the multicast arena at the same offset on every rank (DDP / hvd gradient buckets do).
+// Differences from k_allreduce_nvls, all about the FIXED cost of a call:
+//   * the cross-GPU barrier is a counter in the multicast arena's head: one thread issues ONE
+//     multimem.red.release (the switch adds 1 into all W copies) and spins on its local copy until it
+//     reaches W * epoch — instead of W unicast release-stores and W spinning lanes;
+//   * epochs are per channel, so a CTA never waits for the other CTAs of its own grid: no exit ticket,
+//     no grid-wide counters (channel b only ever meets channel b of the peers);
+//   * small argument block (launch latency grows with the parameter bytes);
+//   * griddepcontrol: launched with programmatic stream serialization, the next kernel of a bucket
+//     train becomes resident while this one drains (its prologue waits for our completion).
+struct B2cNvlsArgs {
+  char* uc;                 // local unicast view of the multicast arena
+  char* mc;                 // multicast view
+  uint32_t* ctl;            // this rank's control page
+  uint32_t* status;         // sticky error words (host mapped)
+  size_t off;               // byte offset of the tensor inside the arena
+  size_t nvec;              // whole 16-byte vectors
+  unsigned long long timeout_ns;
+  float scale;
+  int rank, world;
+  uint32_t chunk_vecs;
+  int acq_poll;             // flag spin: 1 = ld.acquire.sys polls, 0 = relaxed polls + one fence at the end
+};
+
+__device__ __forceinline__ void multimem_red_add_release_u32(void* mc, uint32_t v) {
+  asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// one thread: arrive (+1 in every rank's copy) and wait until all W ranks have arrived `target / W` times.
+// returns false on timeout (sticky status word set).
+template <bool ACQ_POLL>
+__device__ __forceinline__ bool mc_arrive_wait(char* mc_flag, const uint32_t* uc_flag, uint32_t target,
+                                               unsigned long long timeout_ns, uint32_t* status, int channel) {
+  multimem_red_add_release_u32(mc_flag, 1u);
+  unsigned long long t0 = 0;
+  unsigned spins = 0;
+  while ((int)((ACQ_POLL ? ld_acquire_sys(uc_flag) : ld_relaxed_sys_u32(uc_flag)) - target) < 0) {
+    if ((++spins & 0x3ffu) == 0u) {
+      unsigned long long now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > timeout_ns) {
+        volatile uint32_t* st = status;
+        if (st[0] == 0u) {
+          st[1] = target; st[2] = (uint32_t)channel; st[3] = 0xffffffffu;
+          st[0] = (uint32_t)(-B2C_ETIMEOUT);
+          __threadfence_system();
+        }
+        return false;
+      }
+    }
+  }
+  if (!ACQ_POLL) fence_acq_rel_sys();
+  return true;
+}
+
+template <int MODE, int NU, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_nvls_inplace(const __grid_constant__ B2cNvlsArgs a) {
+  __shared__ uint32_t s_epoch;
+  __shared__ int s_dead;
+  const int b = blockIdx.x;
+  char* mc_flag = a.mc + (size_t)b * B2C_MC_FLAG_STRIDE;
+  const uint32_t* uc_flag = reinterpret_cast<const uint32_t*>(a.uc + (size_t)b * B2C_MC_FLAG_STRIDE);
+  unsigned long long* ph = reinterpret_cast<unsigned long long*>(a.ctl) + B2C_CTL_PHASE_U64;
+  const uint32_t W = (uint32_t)a.world;
+  // everything before this line overlaps the tail of the previous kernel on the stream (PDL); the epoch
+  // word below is written by that kernel's last instructions
+  pdl_wait();
+  if (threadIdx.x == 0) {
+    if (b == 0) ph[0] = globaltimer_ns();
+    const uint32_t e = ld_volatile_u32(a.ctl + B2C_CTL_MC_EPOCH + b);
+    s_epoch = e;
+    // barrier A: every rank's gradients are final (stream order before its launch)
+    const bool okA = a.acq_poll ? mc_arrive_wait<true>(mc_flag, uc_flag, (e + 1u) * W, a.timeout_ns, a.status, b)
+                                : mc_arrive_wait<false>(mc_flag, uc_flag, (e + 1u) * W, a.timeout_ns, a.status, b);
+    s_dead = okA ? 0 : 1;
+    if (b == 0) ph[1] = globaltimer_ns();
+  }
+  __syncthreads();
+  pdl_launch_dependents();
+  const bool dead = s_dead != 0;
+  if (!dead) {
+    const size_t nvs = (a.nvec + W - 1) / W;
+    const size_t s0 = (size_t)a.rank * nvs;
+    const size_t sl = (s0 >= a.nvec) ? 0 : ((s0 + nvs <= a.nvec) ? nvs : a.nvec - s0);
+    char* mc = a.mc + a.off + s0 * 16;
+    const size_t step = (size_t)gridDim.x * a.chunk_vecs;
+    for (size_t c0 = (size_t)b * a.chunk_vecs; c0 < sl; c0 += step) {
+      const size_t c1 = (c0 + a.chunk_vecs < sl) ? c0 + a.chunk_vecs : sl;
+      for (size_t i = c0 + threadIdx.x; i < c1; i += (size_t)THREADS * NU) {
+        uint4 v[NU];
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          const size_t j = i + (size_t)u * THREADS;
+          if (j < c1) v[u] = (MODE == MODE_F32) ? multimem_ld_reduce_f32(mc + j * 16) : multimem_ld_reduce_bf16(mc + j * 16);
+        }
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          const size_t j = i + (size_t)u * THREADS;
+          if (j < c1) multimem_st_v4(mc + j * 16, nvls_scale<MODE>(v[u], a.scale));
+        }
+      }
+    }
+  }
+  __syncthreads();  // every multimem.st of this CTA is issued; the release below orders them before the arrival
+  if (threadIdx.x == 0) {
+    const uint32_t e = s_epoch;
+    // barrier B: every rank's results have landed in every copy
+    if (!dead) {
+      if (a.acq_poll) mc_arrive_wait<true>(mc_flag, uc_flag, (e + 2u) * W, a.timeout_ns, a.status, b);
+      else mc_arrive_wait<false>(mc_flag, uc_flag, (e + 2u) * W, a.timeout_ns, a.status, b);
+    }
+    if (b == 0) {
+      const unsigned long long t = globaltimer_ns();
+      ph[2] = t; ph[3] = t;
+      phase_commit(a.ctl);
+    }
+    a.ctl[B2C_CTL_MC_EPOCH + b] = e + 2u;
+  }
+}
+
+
+// ================================================================= fused optimizer step
+// The step on the far side of the path: instead of "allreduce the gradients, then let every rank run the same
+// optimizer over all of them", the rank that reduces a shard also APPLIES the optimizer to that shard — fp32
+// state held for the owned shard only (1/W of the momentum / Adam moments per rank) — and what travels back
+// is the updated WEIGHTS, written into every rank's parameter bucket.  Same NVLink bytes as the allreduce,
+// minus a full read/write pass over gradients, parameters and state on every rank and the optimizer's launches.
+// Arithmetic follows torch.optim.SGD / Adam / AdamW (single-tensor form) operation by operation in fp32.
+enum { B2C_OPT_NONE = 0, B2C_OPT_SGD = 1, B2C_OPT_ADAM = 2, B2C_OPT_ADAMW = 3 };
+
+// Every derived scalar is computed by the host in double and rounded to float ONCE, the way torch's Python
+// optimizers hand their scalars to the kernels (1 - beta2 formed in float would be off by 1e-5 relative).
+struct B2cOptK {
+  int kind, nesterov, first;     // first: momentum buffers are created from the first gradient (torch: buf = clone(g))
+  float lr, momentum, one_m_dampening, weight_decay;
+  float one_m_beta1, beta2, one_m_beta2, eps, step_size /* lr / bias_correction1 */, bc2_sqrt, adamw_keep /* 1 - lr * wd */;
+};
+
+template <int KIND>
+__device__ __forceinline__ float opt_apply(float g, float w, float& s1, float& s2, const B2cOptK& o) {
+  if (KIND == B2C_OPT_SGD) {
+    if (o.weight_decay != 0.f) g = __fmaf_rn(o.weight_decay, w, g);
+    if (o.momentum != 0.f) {
+      s1 = o.first ? g : __fmaf_rn(o.one_m_dampening, g, __fmul_rn(o.momentum, s1));   // buf.mul_(mom).add_(g, alpha=1-damp)
+      g = o.nesterov ? __fmaf_rn(o.momentum, s1, g) : s1;
+    }
+    return __fmaf_rn(-o.lr, g, w);
+  } else {
+    if (KIND == B2C_OPT_ADAMW) w = __fmul_rn(w, o.adamw_keep);                  // param.mul_(1 - lr * wd)
+    else if (o.weight_decay != 0.f) g = __fmaf_rn(o.weight_decay, w, g);
+    s1 = __fmaf_rn(o.one_m_beta1, __fsub_rn(g, s1), s1);                        // exp_avg.lerp_(g, 1 - beta1)
+    s2 = __fmaf_rn(__fmul_rn(o.one_m_beta2, g), g, __fmul_rn(o.beta2, s2));     // exp_avg_sq.mul_(b2).addcmul_(g, g, 1 - b2)
+    const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(s2), o.bc2_sqrt), o.eps);
+    return __fmaf_rn(-o.step_size, __fdiv_rn(s1, denom), w);                   // param.addcdiv_(exp_avg, denom, -step_size)
+  }
+}
+
+// one 16-byte vector of reduced fp32 gradients -> updated weights (fp32 parameters and state)
+template <int KIND>
+__device__ __forceinline__ uint4 opt_vec(uint4 g, uint4 w, float4* s1p, float4* s2p, const B2cOptK& o) {
+  float4 s1 = (KIND == B2C_OPT_SGD && (o.momentum == 0.f || o.first)) ? make_float4(0.f, 0.f, 0.f, 0.f) : *s1p;
+  float4 s2 = (KIND == B2C_OPT_SGD) ? make_float4(0.f, 0.f, 0.f, 0.f) : *s2p;
+  uint4 r;
+  r.x = __float_as_uint(opt_apply<KIND>(__uint_as_float(g.x), __uint_as_float(w.x), s1.x, s2.x, o));
+  r.y = __float_as_uint(opt_apply<KIND>(__uint_as_float(g.y), __uint_as_float(w.y), s1.y, s2.y, o));
+  r.z = __float_as_uint(opt_apply<KIND>(__uint_as_float(g.z), __uint_as_float(w.z), s1.z, s2.z, o));
+  r.w = __float_as_uint(opt_apply<KIND>(__uint_as_float(g.w), __uint_as_float(w.w), s1.w, s2.w, o));
+  if (KIND != B2C_OPT_SGD || o.momentum != 0.f) *s1p = s1;
+  if (KIND != B2C_OPT_SGD) *s2p = s2;
+  return r;
+}
+
+// ---- W = 1: the whole step is local.  Streaming, HBM bound: SGD+momentum reads g, w, m and writes w, m
+// (20 bytes per parameter), Adam reads g, w, m, v and writes w, m, v (28).  Grid fills the chip.
+template <int KIND>
+__global__ void __launch_bounds__(256) k_fused_step_local(const float* __restrict__ grad, float* __restrict__ param,
+                                                          float* __restrict__ st1, float* __restrict__ st2, size_t count,
+                                                          float scale, const __grid_constant__ B2cOptK o) {
+  const size_t nfull = count / 4;
+  const uint4* g4 = reinterpret_cast<const uint4*>(grad);
+  uint4* w4 = reinterpret_cast<uint4*>(param);
+  float4* s1 = reinterpret_cast<float4*>(st1);
+  float4* s2 = reinterpret_cast<float4*>(st2);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nfull; i += stride) {
+    uint4 g = g4[i];
+    if (scale != 1.f) g = nvls_scale<MODE_F32>(g, scale);
+    w4[i] = opt_vec<KIND>(g, w4[i], s1 + i, s2 + i, o);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (count & 3)) {   // ragged tail, element-wise
+    const size_t e = nfull * 4 + threadIdx.x;
+    float a = 0.f, b = 0.f;
+    if (!(KIND == B2C_OPT_SGD && (o.momentum == 0.f || o.first))) a = st1[e];
+    if (KIND != B2C_OPT_SGD) b = st2[e];
+    param[e] = opt_apply<KIND>(__fmul_rn(grad[e], scale), param[e], a, b, o);
+    if (KIND != B2C_OPT_SGD || o.momentum != 0.f) st1[e] = a;
+    if (KIND != B2C_OPT_SGD) st2[e] = b;
+  }
+}
+
+// ---- peer-to-peer (registered buckets, or a local group): zero-copy two-shot whose second shot carries weights.
+// a.buf[q] = rank q's GRADIENT bucket, a.pbuf[q] = rank q's PARAMETER bucket (both mapped here); state is local.
+struct B2cFusedArgs {
+  B2cKArgs k;
+  void* pbuf[B2C_MAX_WORLD];
+  float* st1[B2C_MAX_WORLD];     // per (virtual) rank: state of its shard (real mode: only [rank])
+  float* st2[B2C_MAX_WORLD];
+  B2cOptK opt;
+};
+
+template <int KIND, int W>
+__global__ void __launch_bounds__(512, 1) k_fused_step_zc(const __grid_constant__ B2cFusedArgs fa) {
+  const B2cKArgs& a = fa.k;
+  constexpr int U = (W >= 8) ? 1 : (W >= 4) ? 2 : 4;
+  Ctx c = prologue(a);
+  const size_t nvec = a.count / 4;            // whole vectors only: buckets are padded to 16 bytes by the reducer
+  const size_t nvs = (nvec + W - 1) / W;
+  channel_barrier(a, c, c.epoch + 1u);
+  if (!c.dead) {
+    const size_t s0 = (size_t)c.rank * nvs;
+    const size_t sl = (s0 >= nvec) ? 0 : ((s0 + nvs <= nvec) ? nvs : nvec - s0);
+    char* p[W];
+#pragma unroll
+    for (int q = 0; q < W; ++q) p[q] = static_cast<char*>(a.buf[q]) + s0 * 16;
+    const char* wloc = static_cast<const char*>(fa.pbuf[c.rank]) + s0 * 16;
+    float4* s1 = reinterpret_cast<float4*>(fa.st1[c.rank]);
+    float4* s2 = reinterpret_cast<float4*>(fa.st2[c.rank]);
+    B2C_FOR_OWNED(sl, U, {
+      uint4 v[U][W];
+      uint4 w[U];
+      _Pragma("unroll") for (int u = 0; u < U; ++u)
+        _Pragma("unroll") for (int q = 0; q < W; ++q)
+          if (pred[u]) v[u][q] = ld_sys_v4(p[q] + idx[u] * 16);
+      _Pragma("unroll") for (int u = 0; u < U; ++u) if (pred[u]) w[u] = ld_sys_v4(wloc + idx[u] * 16);
+      _Pragma("unroll") for (int u = 0; u < U; ++u) if (pred[u]) {
+        Acc<MODE_F32> acc; acc.init(v[u][0], a.scale);
+        _Pragma("unroll") for (int q = 1; q < W; ++q) acc.add(v[u][q], a.scale);
+        const uint4 res = opt_vec<KIND>(acc.finish(), w[u], s1 + idx[u], s2 + idx[u], fa.opt);
+        _Pragma("unroll") for (int k = 0; k < W; ++k) {  // own copy first, then peers rotated
+          int q = c.rank + k; if (q >= W) q -= W;
+          st_v4(static_cast<char*>(fa.pbuf[q]) + (s0 + idx[u]) * 16, res);
+        }
+      }
+    })
+  }
+  channel_barrier(a, c, c.epoch + 2u);
+  epilogue(c);
+}
+
+// ---- through the switch: multimem.ld_reduce the gradient shard, update, multimem.st the weights; optionally the
+// root's module buffers (C4, the per-forward broadcast of the reference path) ride in the same launch.
+struct B2cNvlsFusedArgs {
+  B2cNvlsArgs n;          // n.off = gradient bucket offset in the arena
+  size_t param_off;       // parameter bucket offset in the arena (same layout as the gradient bucket)
+  float* st1;
+  float* st2;
+  size_t bcast_off;       // C4 fold: [bcast_off, +bcast_vecs*16) of the arena is multicast from bcast_root
+  size_t bcast_vecs;
+  int bcast_root;
+  B2cOptK opt;
+};
+
+template <int KIND, int NU>
+__global__ void __launch_bounds__(512, 1) k_fused_step_nvls(const __grid_constant__ B2cNvlsFusedArgs fa) {
+  const B2cNvlsArgs& a = fa.n;
+  __shared__ uint32_t s_epoch;
+  __shared__ int s_dead;
+  const int b = blockIdx.x;
+  char* mc_flag = a.mc + (size_t)b * B2C_MC_FLAG_STRIDE;
+  const uint32_t* uc_flag = reinterpret_cast<const uint32_t*>(a.uc + (size_t)b * B2C_MC_FLAG_STRIDE);
+  unsigned long long* ph = reinterpret_cast<unsigned long long*>(a.ctl) + B2C_CTL_PHASE_U64;
+  const uint32_t W = (uint32_t)a.world;
+  pdl_wait();
+  if (threadIdx.x == 0) {
+    if (b == 0) ph[0] = globaltimer_ns();
+    const uint32_t e = ld_volatile_u32(a.ctl + B2C_CTL_MC_EPOCH + b);
+    s_epoch = e;
+    s_dead = mc_arrive_wait<true>(mc_flag, uc_flag, (e + 1u) * W, a.timeout_ns, a.status, b) ? 0 : 1;
+    if (b == 0) ph[1] = globaltimer_ns();
+  }
+  __syncthreads();
+  pdl_launch_dependents();
+  const bool dead = s_dead != 0;
+  if (!dead) {
+    const size_t nvs = (a.nvec + W - 1) / W;
+    const size_t s0 = (size_t)a.rank * nvs;
+    const size_t sl = (s0 >= a.nvec) ? 0 : ((s0 + nvs <= a.nvec) ? nvs : a.nvec - s0);
+    const char* gmc = a.mc + a.off + s0 * 16;
+    char* wmc = a.mc + fa.param_off + s0 * 16;
+    const char* wuc = a.uc + fa.param_off + s0 * 16;
+    float4* s1 = reinterpret_cast<float4*>(fa.st1);
+    float4* s2 = reinterpret_cast<float4*>(fa.st2);
+    const size_t step = (size_t)gridDim.x * a.chunk_vecs;
+    for (size_t c0 = (size_t)b * a.chunk_vecs; c0 < sl; c0 += step) {
+      const size_t c1 = (c0 + a.chunk_vecs < sl) ? c0 + a.chunk_vecs : sl;
+      for (size_t i = c0 + threadIdx.x; i < c1; i += (size_t)blockDim.x * NU) {
+        uint4 g[NU], w[NU];
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          const size_t j = i + (size_t)u * blockDim.x;
+          if (j < c1) { g[u] = multimem_ld_reduce_f32(gmc + j * 16); w[u] = ld_sys_v4(wuc + j * 16); }
+        }
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          const size_t j = i + (size_t)u * blockDim.x;
+          if (j < c1) multimem_st_v4(wmc + j * 16, opt_vec<KIND>(nvls_scale<MODE_F32>(g[u], a.scale), w[u], s1 + j, s2 + j, fa.opt));
+        }
+      }
+    }
+    if (fa.bcast_vecs && a.rank == fa.bcast_root) {   // C4: the root's buffer bytes, in place, to every rank
+      const char* src = a.uc + fa.bcast_off;
+      char* dst = a.mc + fa.bcast_off;
+      for (size_t i = (size_t)b * blockDim.x + threadIdx.x; i < fa.bcast_vecs; i += (size_t)gridDim.x * blockDim.x)
+        multimem_st_v4(dst + i * 16, ld_sys_v4(src + i * 16));
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t e = s_epoch;
+    if (!dead) mc_arrive_wait<true>(mc_flag, uc_flag, (e + 2u) * W, a.timeout_ns, a.status, b);
+    if (b == 0) {
+      const unsigned long long t = globaltimer_ns();
+      ph[2] = t; ph[3] = t;
+      phase_commit(a.ctl);
+    }
+    a.ctl[B2C_CTL_MC_EPOCH + b] = e + 2u;
+  }
 }
 
 

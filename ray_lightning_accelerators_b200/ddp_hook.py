@@ -60,8 +60,13 @@ class B2cHookState:
     def prepare(self, index, buf):
         comm = self.comm
         wire = self.wire_dtype if (self.wire_dtype is not None and buf.dtype == torch.float32) else None
+        old = self._prepared.get(index)
+        if old is not None and old[0] != buf.data_ptr():
+            comm.deregister_ptr(old[0], old[6])  # torch rebuilt its buckets: the old buffer is gone
         if self.register_buckets and not comm.in_nvls_arena(buf):
-            comm.register(buf)  # collective; once per bucket buffer
+            # collective over the comm's private side channel (never the training loop's communicator);
+            # once per bucket buffer, and again on every rank when torch re-allocates its buckets
+            comm.register(buf)
         from .comm import _check_tensor, _wire
         _check_tensor(buf)
         d, w = _wire(buf, wire)
@@ -177,7 +182,16 @@ class BufferSync:
         for b in bufs:
             offs.append(total)
             total += (b.numel() * b.element_size() + 15) // 16 * 16
-        self.flat = torch.zeros(total, dtype=torch.uint8, device=bufs[0].device)
+        # inside the multicast arena when it is up: the root then multicasts the bytes in place (one launch,
+        # nothing copied on the receiving side)
+        self.flat = None
+        if getattr(comm, "nvls_enabled", False):
+            try:
+                self.flat = comm.nvls_empty(total, torch.uint8).zero_()
+            except MemoryError:
+                self.flat = None
+        if self.flat is None:
+            self.flat = torch.zeros(total, dtype=torch.uint8, device=bufs[0].device)
         with torch.no_grad():
             for b, off in zip(bufs, offs):
                 nb = b.numel() * b.element_size()
@@ -200,11 +214,92 @@ def _want_nvls(comm):
     return comm.world >= 4
 
 
+class B2cDataParallel(torch.nn.Module):
+    """Data-parallel wrapper with b2c's own gradient reducer (reducer.B2cReducer) instead of torch's c10d
+    Reducer: what the reference's workers get from DistributedDataParallel(model, device_ids,
+    find_unused_parameters=True) (PTL 1.1.7 configure_ddp, reached from ray_ddp.py:218-219), with the same
+    observable behaviour — parameters and buffers start as rank 0's (C2), buffers follow rank 0 before every
+    forward (C4), after backward every ``.grad`` holds the average over ranks (C3), ``no_sync()`` skips the
+    reduction, unused parameters are tolerated — and none of its per-step overheads: gradients accumulate
+    straight into the communication buckets (no copy-in / copy-out), no NCCL collective of any kind runs
+    inside a step (torch's Reducer allreduces a used-parameter bitmap per step), and nothing blocks the host.
+
+    Difference to torch DDP that a user can see: the gradient of a parameter that took no part in a backward
+    pass is a tensor of zeros (torch leaves it ``None`` when it is unused on every rank)."""
+
+    _is_b2c_data_parallel = True   # unwrapped like DistributedDataParallel by the trainer (mini_pl.Trainer.get_model)
+
+    def __init__(self, module, comm, bucket_cap_mb=25, root=0, sync_states=True):
+        super().__init__()
+        from .reducer import B2cReducer
+        self.module = module
+        self.comm = comm
+        if sync_states:
+            broadcast_module_states(comm, module, root=root)       # C2
+        if comm.world > 1 and _want_nvls(comm) and not comm.nvls_enabled:
+            grad_bytes = sum(p.numel() * p.element_size() for p in module.parameters() if p.requires_grad)
+            comm.enable_nvls(int(os.environ.get("B2C_NVLS_ARENA_BYTES", 2 * grad_bytes + (96 << 20))))
+        if comm.world > 1:
+            comm.autotune()                                         # measured crossover table, once per comm
+        self.bufsync = BufferSync(comm, module, root=root)          # C4 (buffers re-pointed into one flat tensor)
+        self.reducer = B2cReducer(module.parameters(), comm, op_average=True, bucket_cap_bytes=int(bucket_cap_mb) << 20)
+        self.require_backward_grad_sync = True
+        self._c4_folded = False        # set by fuse_optimizer: the buffer broadcast rides in the last bucket's launch
+        self._buffers_synced = False
+
+    def fuse_optimizer(self, optimizer):
+        """Fold `optimizer`'s step into the bucket launches (fused.FusedOptimizer); returns the object to use in
+        its place.  Falls back to the optimizer itself when it is of an unsupported kind."""
+        from . import fused
+        if not fused.supported(optimizer):
+            return optimizer
+        return fused.FusedOptimizer(optimizer, self)
+
+    def forward(self, *args, **kwargs):
+        if self.training:
+            if self.bufsync.flat is not None:
+                if self._c4_folded and self._buffers_synced:
+                    self._buffers_synced = False   # already replicated by the last fused step of the previous backward
+                else:
+                    self.bufsync()
+            if torch.is_grad_enabled():
+                self.reducer.rearm()
+        return self.module(*args, **kwargs)
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Accumulate gradients locally; the next backward outside the context reduces the sum (DDP.no_sync)."""
+        old = self.reducer._enabled
+        self.reducer._enabled = False
+        try:
+            yield
+        finally:
+            self.reducer._enabled = old
+
+    def zero_grad(self, set_to_none=False):
+        self.reducer.zero_grad()
+
+    # bench / tests: per-bucket device times
+    @property
+    def _b2c_state(self):
+        return self.reducer
+
+    def close(self):
+        self.reducer.close()
+
+
 def wrap_ddp(model, comm, device_ids=None, wire_dtype=None, find_unused_parameters=True,
-             bucket_cap_mb=25, gradient_as_bucket_view=False, process_group=None):
-    """Build the DDP wrapper the way the reference's workers do (PTL 1.1.7 configure_ddp:
+             bucket_cap_mb=25, gradient_as_bucket_view=False, process_group=None, reducer=None):
+    """Build the data-parallel wrapper the way the reference's workers do (PTL 1.1.7 configure_ddp:
     DistributedDataParallel(model, device_ids, find_unused_parameters=True), reached from
-    ray_ddp.py:218-219) with the three collectives re-routed to b2c."""
+    ray_ddp.py:218-219) with the three collectives re-routed to b2c.
+
+    reducer="b2c" (default; B2C_REDUCER overrides): B2cDataParallel, b2c's own bucket reducer.
+    reducer="torch": torch's DistributedDataParallel with a comm hook per bucket (kept for the bf16-wire mode and
+    as the like-for-like comparison against stock DDP)."""
+    reducer = reducer or os.environ.get("B2C_REDUCER", "b2c")
+    if reducer == "b2c" and wire_dtype is None:
+        return B2cDataParallel(model, comm, bucket_cap_mb=bucket_cap_mb)
     from torch.nn.parallel import DistributedDataParallel as DDP
     broadcast_module_states(comm, model, root=0)                 # C2 (instead of init_sync)
     bufsync = BufferSync(comm, model, root=0)                    # C4 set-up (re-points buffers)

@@ -96,7 +96,11 @@ def join():
 def allreduce_(tensor, op=Average, name=None):
     _need()
     scale = 1.0 / _st["size"] if op == Average else 1.0
-    if _st["comm"] is not None and tensor.is_cuda and tensor.dtype in (torch.float32, torch.bfloat16):
+    if _st["comm"] is not None and tensor.is_cuda:
+        if tensor.dtype not in (torch.float32, torch.bfloat16):
+            # no silent detour through NCCL: the GPU path is libb2c.so or nothing
+            raise TypeError(f"hvd.allreduce on GPU supports float32 / bfloat16 tensors, got {tensor.dtype}; "
+                            f"cast first (metrics: .float())")
         _st["comm"].allreduce(tensor, scale=scale)
     elif _st["size"] > 1:
         dist.all_reduce(tensor)
@@ -164,110 +168,54 @@ def broadcast_optimizer_state(optimizer, root_rank=0):
 
 class DistributedOptimizer:
     """hvd.DistributedOptimizer(optimizer, named_parameters=...): gradients are averaged across
-    ranks before step().  Gradients are views into static flat buckets filled in reverse
-    parameter order; a bucket is reduced (on a high-priority side stream) as soon as the last
-    of its gradients has been accumulated, overlapping the rest of backward; synchronize()
-    makes the current stream wait for all of them."""
+    ranks before step().  Built on reducer.B2cReducer — the same bucket reducer the DDP path uses:
+    gradients are views into static flat buckets (inside the NVLink-multicast arena from 4 ranks up,
+    registered with every peer below that); a bucket is reduced on the comm's side stream as soon as the
+    last of its gradients has been accumulated and every earlier bucket has been launched (fixed order on
+    every rank), overlapping the rest of backward; synchronize() launches what is left and makes the
+    current stream wait."""
 
-    def __init__(self, optimizer, named_parameters=None, op=Average, bucket_bytes=None):
+    def __init__(self, optimizer, named_parameters=None, op=Average, bucket_bytes=None, backward_passes_per_step=1):
         _need()
+        from .reducer import B2cReducer
         self._opt = optimizer
         self._op = op
         self._skip_sync = False
-        self._synced = True
+        self._passes_per_step = int(backward_passes_per_step)
         params = [p for g in optimizer.param_groups for p in g["params"] if p.requires_grad]
         self._params = params
-        self._buckets = []          # (flat, [params])
-        self._bucket_of = {}
-        self._handles = []
-        self._stream = torch.cuda.Stream(priority=-1) if _st["comm"] is not None else None
-        cap = bucket_bytes or _BUCKET_BYTES
         comm = _st["comm"]
         if comm is not None and params:
             from .ddp_hook import _want_nvls
-            if _want_nvls(comm):
+            if _want_nvls(comm) and not comm.nvls_enabled:
                 # from ~4 ranks up the gradient buckets live in the NVLink-multicast arena and are
                 # reduced in the switch, in place (collective set-up, once)
                 total = sum(p.numel() * p.element_size() for p in params)
-                comm.enable_nvls(int(os.environ.get("B2C_NVLS_ARENA_BYTES", 2 * total + (64 << 20))))
-        run, nbytes, key = [], 0, None
-        for p in reversed(params):
-            k = (p.dtype, p.device)
-            pb = p.numel() * p.element_size()
-            if run and (k != key or nbytes + pb > cap):
-                self._make_bucket(run)
-                run, nbytes = [], 0
-            key = k
-            run.append(p)
-            nbytes += pb
-        if run:
-            self._make_bucket(run)
-        for p in params:
-            self._handles.append(p.register_post_accumulate_grad_hook(self._on_grad))
-        self._ready = [0] * len(self._buckets)
-        self._launched = [False] * len(self._buckets)
+                comm.enable_nvls(int(os.environ.get("B2C_NVLS_ARENA_BYTES", 2 * total + (96 << 20))))
+        if comm is not None and comm.world > 1:
+            comm.autotune()      # measured crossover table, once per comm
+        cap = bucket_bytes or _BUCKET_BYTES
 
-    def _make_bucket(self, run):
-        # 16-byte aligned slices so that every gradient is a legal vector-load target
-        offs, total = [], 0
-        es = run[0].element_size()
-        for p in run:
-            offs.append(total)
-            total += (p.numel() * es + 15) // 16 * 16 // es
-        comm = _st["comm"]
-        flat = None
-        if comm is not None and run[0].is_cuda and comm.nvls_enabled:
-            try:
-                flat = comm.nvls_empty(total, run[0].dtype).zero_()
-            except MemoryError:
-                flat = None
-        if flat is None:
-            flat = torch.zeros(total, dtype=run[0].dtype, device=run[0].device)
-        for p, off in zip(run, offs):
-            p.grad = flat[off:off + p.numel()].view_as(p)
-            p._b2c_grad_view = p.grad
-            self._bucket_of[p] = len(self._buckets)
-        if comm is not None and flat.is_cuda and not comm.in_nvls_arena(flat):
-            comm.register(flat)  # zero-copy from the first step on (collective)
-        self._buckets.append((flat, list(run)))
+        def gloo_allreduce(flat, scale):
+            if _st["size"] > 1:
+                dist.all_reduce(flat)
+                if scale != 1.0:
+                    flat.mul_(scale)
 
-    def _on_grad(self, p):
-        view = p._b2c_grad_view
-        if p.grad is not view:  # someone replaced the gradient tensor (zero_grad(set_to_none=True))
-            view.copy_(p.grad)
-            p.grad = view
-        b = self._bucket_of[p]
-        self._ready[b] += 1
-        self._synced = False
-        if self._ready[b] == len(self._buckets[b][1]):
-            self._launch(b)
+        self._red = B2cReducer(params, comm, op_average=(op == Average), bucket_cap_bytes=cap, first_bucket_bytes=cap,
+                               fallback_allreduce=gloo_allreduce, world=_st["size"])
+        # Horovod semantics: the reduction is completed by synchronize() / step(), not by the end of backward
+        self._red._finalize_at_backward_end = False
+        self._buckets = [(b.flat, b.params) for b in self._red.buckets]
 
-    def _launch(self, b):
-        if self._launched[b]:
-            return
-        self._launched[b] = True
-        flat = self._buckets[b][0]
-        if _st["size"] == 1:
-            return
-        scale = 1.0 / _st["size"] if self._op == Average else 1.0
-        if _st["comm"] is not None and flat.is_cuda:
-            self._stream.wait_stream(torch.cuda.current_stream())
-            _st["comm"].allreduce(flat, scale=scale, stream=self._stream)
-        else:
-            dist.all_reduce(flat)
-            if self._op == Average:
-                flat.div_(_st["size"])
+    @property
+    def _synced(self):
+        return not (self._red._grads_seen or any(b.launched for b in self._red.buckets))
 
     def synchronize(self):
         """Wait for every gradient allreduce.  Buckets whose gradients never all arrived (unused
         parameters) are reduced now, with whatever they hold (zeros), like Horovod does."""
-        for b in range(len(self._buckets)):
-            self._launch(b)
-        if self._stream is not None:
-            torch.cuda.current_stream().wait_stream(self._stream)
-        self._ready = [0] * len(self._buckets)
-        self._launched = [False] * len(self._buckets)
-        self._synced = True
+        self._red.flush()
 
     @contextlib.contextmanager
     def skip_synchronize(self):
@@ -283,8 +231,7 @@ class DistributedOptimizer:
         return self._opt.step(closure) if closure is not None else self._opt.step()
 
     def zero_grad(self, set_to_none=False):
-        for flat, _ in self._buckets:  # one memset per bucket; gradients stay views
-            flat.zero_()
+        self._red.zero_grad()  # one memset per bucket; gradients stay views
 
     @property
     def param_groups(self):

@@ -182,7 +182,7 @@ class Trainer:
 
     def get_model(self):
         m = self.model
-        while isinstance(m, (torch.nn.parallel.DistributedDataParallel, StepModule)):
+        while isinstance(m, (torch.nn.parallel.DistributedDataParallel, StepModule)) or getattr(m, "_is_b2c_data_parallel", False):
             m = m.module
         return m
 

@@ -101,10 +101,18 @@ class RayAccelerator:
             if torch.cuda.is_available():
                 torch.cuda.empty_cache()
 
-        ray.get([w.execute.remote(shutdown_remote) for w in self.workers])
-        for w in self.workers:
-            ray.kill(w, no_restart=True)
-        self.workers = []
+        # Graceful only when training ended normally: after a worker failure its peers may still sit in a control
+        # collective and would never reach shutdown_remote — kill them instead of waiting for a watchdog, so the
+        # original exception is what the user sees.
+        try:
+            if not getattr(self, "_failed", False):
+                ray.get([w.execute.remote(shutdown_remote) for w in self.workers], timeout=60)
+        except Exception:  # noqa: BLE001
+            pass
+        finally:
+            for w in self.workers:
+                ray.kill(w, no_restart=True)
+            self.workers = []
 
     def __getstate__(self):
         # actor handles never travel to the workers (intent of ray_ddp.py:123-130)
@@ -147,9 +155,13 @@ class RayAccelerator:
 
         futures = [self.workers[i].execute.remote(self.train_remote, trainer_ref, i, queue)
                    for i in range(self.num_workers)]
-        results = process_results(futures, queue)
+        self._failed = True
+        try:
+            results = process_results(futures, queue)
+            self._failed = False
+        finally:
+            self.trainer = trainer   # also on failure: the caller's Trainer keeps its accelerator usable
         results, best_path, state_dict = results[0]
-        self.trainer = trainer
         self.trainer.model.load_state_dict(state_dict)
         if self.trainer.checkpoint_callback:
             self.trainer.checkpoint_callback.best_model_path = best_path
@@ -182,6 +194,9 @@ class RayAccelerator:
         optimizers, schedulers = _init_optimizers(model)
         device_ids = self.get_device_ids()
         wrapped = self.configure_ddp(model, device_ids)
+        if self.use_gpu and os.environ.get("B2C_FUSED_OPT", "0") == "1" and hasattr(wrapped, "fuse_optimizer"):
+            # opt-in: optimizer.step() folded into the bucket launches (fused.FusedOptimizer)
+            optimizers = [wrapped.fuse_optimizer(o) for o in optimizers]
         device = torch.device("cuda", self.trainer.root_gpu) if self.use_gpu else torch.device("cpu")
         results = self.trainer.run_training(wrapped, model, optimizers, schedulers, device)
         self.transfer_distrib_spawn_state_on_fit_end(model, mp_queue, results)

@@ -67,12 +67,3 @@ def pin_gpu(use_gpu: bool, local_rank: int = 0) -> Optional[int]:
     idx = 0 if n == 1 else int(local_rank) % n
     torch.cuda.set_device(idx)
     return idx
-
-
-def exchange_ipc_handles(blob: bytes, rank: int, world: int, group=None):
-    """All ranks' 256-byte export blobs in rank order, over the torch process group the
-    accelerator has already initialised (control plane: W x 256 bytes, once per fit)."""
-    import torch.distributed as dist
-    out = [None] * world
-    dist.all_gather_object(out, blob, group=group)
-    return out

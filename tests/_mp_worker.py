@@ -113,38 +113,105 @@ def main():
     comm.set_param(_lib.PARAM_ZEROCOPY, 1)
     comm.set_param(_lib.PARAM_TWOSHOT_VARIANT, 0)
     # ---- NVLS (in-switch reduction) when the box supports NVLink multicast
-    nvls = comm.enable_nvls(64 << 20)
+    nvls = comm.enable_nvls(96 << 20)
     if rank == 0:
         print(f"NVLS enabled={nvls} err={comm.nvls_error}")
     if nvls:
         from ray_lightning_accelerators_b200.comm import ALGO_NVLS
-        for kind in ("int", "randn"):
-            for n in (1, 5, 1000, 27882, 3103747):
-                grads = [O.payload(kind, n, r) for r in range(world)]
-                ref = torch.from_numpy(grads[rank]).to(dev).div_(world)
-                dist.all_reduce(ref)
-                denom = sum(np.abs(x.astype(np.float64)) for x in grads) / world
-                for inplace in (False, True):
-                    if inplace:
-                        t = comm.nvls_empty(n)
-                        t.copy_(torch.from_numpy(grads[rank]))
-                    else:
-                        t = torch.from_numpy(grads[rank]).to(dev)
-                    z0 = comm.stats()["nvls_launches"]
-                    comm.allreduce(t, algo=ALGO_NVLS)
+        def nvls_close(got, ref, grads_):
+            """NVLS sums first and scales after, in the switch's own order: same NaN / inf classes as the
+            reference (div then sum) wherever the unscaled sum cannot overflow, values within 1e-6 of
+            sum|g|/W (plus one fp32 denormal step: the switch may flush denormals)."""
+            mag = sum(np.abs(x.astype(np.float64)) for x in grads_)
+            safe = mag < 3.0e38
+            assert np.array_equal(np.isnan(got[safe]), np.isnan(ref[safe])), "NaN classes differ"
+            fin = safe & np.isfinite(ref)
+            assert np.isfinite(got[fin]).all(), "inf where the reference is finite"
+            err = np.abs(got[fin].astype(np.float64) - ref[fin].astype(np.float64))
+            assert (err <= 1e-6 * mag[fin] / world + 1.2e-38).all(), float(err.max())
+            inf = safe & np.isinf(ref)
+            assert np.array_equal(got[inf], ref[inf]), "inf classes differ"
+
+        empty = torch.empty(0, device=dev)
+        comm.allreduce(empty, algo=ALGO_NVLS)  # size 0: accepted, nothing launched
+        for lean in (1, 0):
+            comm.set_param(_lib.PARAM_NVLS_LEAN, lean)
+            for kind in ("int", "randn", "wide", "special"):
+                for n in (1, 5, 1000, 27882, 3103747):
+                    grads = [O.payload(kind, n, r) for r in range(world)]
+                    ref = torch.from_numpy(grads[rank]).to(dev).div_(world)
+                    dist.all_reduce(ref)
+                    denom = sum(np.abs(x.astype(np.float64)) for x in grads) / world
+                    for inplace in (False, True):
+                        if inplace:
+                            t = comm.nvls_empty(n)
+                            t.copy_(torch.from_numpy(grads[rank]))
+                        else:
+                            if lean == 0:
+                                continue  # the staged kernel is the same in both settings
+                            t = torch.from_numpy(grads[rank]).to(dev)
+                        z0 = comm.stats()["nvls_launches"]
+                        comm.allreduce(t, algo=ALGO_NVLS)
+                        torch.cuda.synchronize()
+                        comm.check_alive()
+                        st_ = comm.stats()
+                        assert st_["last_algo"] == ALGO_NVLS
+                        assert st_["nvls_launches"] > z0 or (inplace and n < 4)  # in place, < 1 vector: all tail
+                        got = t.cpu().numpy()
+                        if kind == "int" and world in (2, 4, 8):
+                            assert torch.equal(bits(t), bits(ref)), ("nvls int bit-exact", n, inplace, lean)
+                        elif kind == "special":
+                            nvls_close(got, ref.cpu().numpy(), grads)
+                        else:
+                            assert O.rel_err(got, ref.cpu().numpy(), denom) <= 1e-6, ("nvls 1e-6", kind, n, inplace, lean)
+                        t0 = t.clone()
+                        dist.broadcast(t0, src=0)
+                        assert torch.equal(bits(t0), bits(t)), "nvls replicas differ"
+                        if inplace:
+                            comm.nvls_free(t)
+        comm.set_param(_lib.PARAM_NVLS_LEAN, 1)
+        # 256-thread build of the lean kernel (the one that fits beside backward kernels)
+        comm.set_param(_lib.PARAM_THREADS_NVLS, 256)
+        for n in (1000, 3103747):
+            grads = [O.payload("int", n, r) for r in range(world)]
+            t = comm.nvls_empty(n)
+            t.copy_(torch.from_numpy(grads[rank]))
+            comm.allreduce(t, algo=ALGO_NVLS)
+            torch.cuda.synchronize()
+            if world in (2, 4, 8):
+                assert np.array_equal(t.cpu().numpy().view(np.uint32), O.b2c_allreduce_f32(grads).view(np.uint32))
+            comm.nvls_free(t)
+        comm.set_param(_lib.PARAM_THREADS_NVLS, 512)
+        # broadcast through the switch: bit-exact vs NCCL for every root, staged and in place, NaN bits included
+        for n in (1, 17, 212904, (5 << 20) + 3):
+            for root in range(world):
+                src = torch.from_numpy(np.random.default_rng(100 * root + rank).integers(0, 256, n, dtype=np.uint8)).to(dev)
+                a, b = src.clone(), src.clone()
+                dist.broadcast(a, src=root)
+                m0 = comm.stats()["bcast_mc_launches"]
+                comm.broadcast(b, root=root)
+                torch.cuda.synchronize()
+                assert comm.stats()["bcast_mc_launches"] > m0, "broadcast did not go through the switch"
+                assert torch.equal(a, b), ("mc broadcast", n, root)
+                if n >= 16:
+                    m = n // 16 * 16
+                    c_ = comm.nvls_empty(m, dtype=torch.uint8)
+                    c_.copy_(src[:m])
+                    comm.broadcast(c_, root=root)
                     torch.cuda.synchronize()
-                    comm.check_alive()
-                    st_ = comm.stats()
-                    assert st_["last_algo"] == ALGO_NVLS
-                    assert st_["nvls_launches"] > z0 or (inplace and n < 4)  # in place, < 1 vector: all tail
-                    got = t.cpu().numpy()
-                    if kind == "int" and world in (2, 4, 8):
-                        assert torch.equal(bits(t), bits(ref)), ("nvls int bit-exact", n, inplace)
-                    else:
-                        assert O.rel_err(got, ref.cpu().numpy(), denom) <= 1e-6, ("nvls 1e-6", kind, n, inplace)
-                    t0 = t.clone()
-                    dist.broadcast(t0, src=0)
-                    assert torch.equal(bits(t0), bits(t)), "nvls replicas differ"
+                    assert torch.equal(a[:m], c_), ("mc broadcast in place", n, root)
+                    comm.nvls_free(c_)
+        # the arena allocator: frees coalesce, and the same call sequence gives the same offsets on every rank
+        p1, p2, p3 = comm.nvls_empty(1000), comm.nvls_empty(70000), comm.nvls_empty(1000)
+        off2 = p2.data_ptr() - comm._nvls_base
+        comm.nvls_free(p2)
+        p4 = comm.nvls_empty(60000)
+        assert p4.data_ptr() - comm._nvls_base == off2, "first fit must reuse the freed block"
+        offs = [None] * world
+        dist.all_gather_object(offs, (p1.data_ptr() - comm._nvls_base, off2, p3.data_ptr() - comm._nvls_base))
+        assert all(o == offs[0] for o in offs), "arena offsets differ across ranks"
+        for t_ in (p4, p3, p1):
+            comm.nvls_free(t_)
         # a ragged slice inside the arena: its neighbours must not be touched by the in-place kernel
         big = comm.nvls_empty(4096)
         big.fill_(7.0)
@@ -156,6 +223,7 @@ def main():
         assert bool((big[1003:] == 7.0).all()), "NVLS in place wrote past the end of the tensor"
         if world in (2, 4, 8):
             assert np.array_equal(sl.cpu().numpy().view(np.uint32), O.b2c_allreduce_f32(grads).view(np.uint32))
+        comm.nvls_free(big)
         gb = [O.to_bf16_bits(O.payload("randn", 1 << 20, r)) for r in range(world)]
         t = torch.from_numpy(gb[rank].view(np.int16).copy()).to(dev).view(torch.bfloat16)
         comm.allreduce(t, algo=ALGO_NVLS)
@@ -185,10 +253,10 @@ def main():
     if world > 2:
         comm.set_param(_lib.PARAM_NVLS_MIN_BYTES, 1024)  # the MLP's 111 KB bucket goes through the switch too
     # ---- DDP: our hook vs stock NCCL DDP, MLP (config #2) 100 steps, loss within 1e-5 relative
-    def train(use_b2c):
+    def train(use_b2c, reducer="b2c"):
         model = workloads.build_model("mnist_mlp", seed=0).to(dev)
         if use_b2c:
-            ddp = ddp_hook.wrap_ddp(model, comm, device_ids=[local])
+            ddp = ddp_hook.wrap_ddp(model, comm, device_ids=[local], reducer=reducer)
         else:
             ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], find_unused_parameters=True)
         opt = model.configure_optimizers()
@@ -215,6 +283,12 @@ def main():
     p0 = p_b2c.clone()
     dist.broadcast(p0, src=0)
     assert torch.equal(p0, p_b2c), "replicas drifted"
+    # the same through torch's own Reducer with the b2c comm hook (the like-for-like arm against stock DDP)
+    l_hook, p_hook = train(True, reducer="torch")
+    rel = np.abs(l_hook - l_ref) / np.maximum(np.abs(l_ref), 1e-12)
+    assert rel.max() <= 1e-5, f"hook path: loss curve differs from NCCL DDP: {rel.max()}"
+    if world == 2:
+        assert np.array_equal(l_hook, l_ref) and torch.equal(p_hook, p_ref)
     # ---- a model with buffers: BatchNorm stats follow rank 0 (C4) like stock DDP
     def train_bn(use_b2c):
         torch.manual_seed(0)

@@ -149,3 +149,39 @@ def test_wire_bf16_matches_torch_compress_semantics():
     exact = O.exact_mean_f64(q)
     assert O.rel_err(mine, exact, denom) <= 2.0 ** -8
     assert O.rel_err(mine, exact, denom) <= O.rel_err(ref, exact, denom) + 1e-12
+
+
+# ------------------------------------------------------------------ fused optimizer step: restatement pinned to torch.optim
+OPT_CASES = [
+    ("sgd", dict(lr=0.1, momentum=0.9)),
+    ("sgd", dict(lr=0.05, momentum=0.0, weight_decay=1e-3)),
+    ("sgd", dict(lr=0.1, momentum=0.8, dampening=0.1, weight_decay=1e-4)),
+    ("sgd", dict(lr=0.1, momentum=0.9, nesterov=True)),
+    ("adam", dict(lr=0.1, betas=(0.9, 0.999), eps=1e-8)),
+    ("adam", dict(lr=1e-3, betas=(0.8, 0.99), eps=1e-6, weight_decay=1e-2)),
+    ("adamw", dict(lr=1e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2)),
+]
+
+
+@pytest.mark.parametrize("kind,cfg", OPT_CASES)
+def test_fused_step_restatement_is_pinned_to_torch_optim(kind, cfg):
+    """oracle.fused_step_f32 restates the optimizer epilogue of the fused kernels; the real upstream optimizers
+    (what the reference's PTL loop calls after the allreduce) pin it: SGD bit for bit, Adam / AdamW within 1e-6
+    relative (+ 1e-6 of a learning-rate step) over five steps."""
+    import torch
+    n = 27884
+    w0 = O.payload("randn", n, 77)
+    p = torch.nn.Parameter(torch.from_numpy(w0.copy()))
+    opt = {"sgd": torch.optim.SGD, "adam": torch.optim.Adam, "adamw": torch.optim.AdamW}[kind]([p], **cfg)
+    w, s1, s2 = w0.copy(), np.zeros(n, np.float32), np.zeros(n, np.float32)
+    for t in range(1, 6):
+        g = O.payload("wide" if t == 3 else "randn", n, 3, seed=100 * t)
+        p.grad = torch.from_numpy(g.copy())
+        opt.step()
+        O.fused_step_f32(kind, cfg, t, g, w, s1, s2)
+        ref = p.detach().numpy()
+        if kind == "sgd":
+            assert np.array_equal(w.view(np.uint32), ref.view(np.uint32)), (kind, cfg, t)
+        else:
+            err = np.abs(w.astype(np.float64) - ref.astype(np.float64))
+            assert (err <= 1e-6 * np.abs(ref) + 1e-6 * cfg["lr"]).all(), (kind, cfg, t, float(err.max()))

@@ -94,3 +94,17 @@ def test_sizes_beyond_the_built_in_scratch_are_refused():
     nine = (ctypes.c_void_p * 9)(*[ok[0].data_ptr()] * 9)
     assert lib.b2c_allreduce_local_noalloc(nine, 9, 4, _lib.F32, ctypes.c_float(1.0), None) == _lib.E_INVAL
     assert lib.b2c_allreduce_local_noalloc(nine, 2, 4, _lib.U8, ctypes.c_float(1.0), None) == _lib.E_UNSUPPORTED
+
+
+def test_barrier_timeout_status_can_be_read_back_and_is_clear_after_good_calls():
+    """The entry point only enqueues, so a flag-barrier timeout inside its kernel is reported through
+    b2c_noalloc_status (sticky words that the per-call wipe of the scratch array does not touch)."""
+    torch.cuda.set_device(0)
+    lib = _lib.load()
+    ts = [torch.full((1000,), float(r), device=DEV) for r in range(4)]
+    assert _noalloc(ts, _lib.F32, 0.25) == 0, _lib.last_error()
+    words = (ctypes.c_uint32 * 4)()
+    assert lib.b2c_noalloc_status(ctypes.byref(words), 0) == 0, _lib.last_error()   # waits for the device
+    assert list(words) == [0, 0, 0, 0]
+    assert float(ts[2][17]) == 1.5
+    assert lib.b2c_noalloc_status(None, 1) == 0
