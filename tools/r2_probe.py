@@ -115,8 +115,9 @@ def main():
         print("lean parity ok", flush=True)
 
     # ---------------- allreduce fixed cost
-    configs = [("r1", dict(lean=0, pdl=0, th=512)), ("lean", dict(lean=1, pdl=0, th=512)),
-               ("lean+pdl", dict(lean=1, pdl=1, th=512)), ("lean+pdl t256", dict(lean=1, pdl=1, th=256))]
+    configs = [("r1", dict(lean=0, pdl=0, th=512, acq=1)), ("lean", dict(lean=1, pdl=0, th=512, acq=1)),
+               ("lean+pdl", dict(lean=1, pdl=1, th=512, acq=1)), ("lean+pdl t256", dict(lean=1, pdl=1, th=256, acq=1)),
+               ("lean+pdl relaxed-poll", dict(lean=1, pdl=1, th=512, acq=0))]
     for S in [int(x) for x in args.sizes.split(",")]:
         n = S // 4
         k = max(2, (160 << 20) // S + 1) if S >= (1 << 20) else 8
@@ -134,6 +135,7 @@ def main():
             comm.set_param(_lib.PARAM_NVLS_LEAN, cfg["lean"])
             comm.set_param(_lib.PARAM_PDL, cfg["pdl"])
             comm.set_param(_lib.PARAM_THREADS_NVLS, cfg["th"])
+            comm.set_param(_lib.PARAM_MC_ACQ_POLL, cfg["acq"])
             us, ph = isolated(lambda: comm.allreduce(bufs[0], algo=ALGO_NVLS), phases=True)
             tr = train(bufs, lambda t_: comm.allreduce(t_, algo=ALGO_NVLS))
             emit(dict(op="allreduce", cfg=name, bytes=S, us=us, us_train=tr, busbw=bus / us / 1e3, busbw_train=bus / tr / 1e3,
@@ -150,6 +152,7 @@ def main():
     comm.set_param(_lib.PARAM_NVLS_LEAN, 1)
     comm.set_param(_lib.PARAM_PDL, 1)
     comm.set_param(_lib.PARAM_THREADS_NVLS, 512)
+    comm.set_param(_lib.PARAM_MC_ACQ_POLL, 1)
     comm.check_alive()
 
     # ---------------- broadcast
