@@ -119,7 +119,7 @@ def run_reference(args):
         "impl": "reference", "metric": "train_samples_per_sec", "value": sps, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": r["seconds"] / steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.model} synthetic 224x224, SGD momentum, torch DDP 25 MB buckets (BASELINE configs[2]); "
+        "config": {"workload": f"{_workload_name(args.model)}, torch DDP 25 MB buckets; "
                                f"GPU arm batch {args.batch}/GPU, CPU reference arm batch {batch}/worker",
                    "global_batch": batch * world, "parallelism": f"dp{world}", "backend": "gloo"},
         "cpu_baseline": {"value": sps, "unit": "samples/s", "cores": threads * world, "kind": "reference",
@@ -131,6 +131,12 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------- b2c arm (GPU)
+def _workload_name(model):
+    return {"resnet50": "resnet50 synthetic 224x224 fp32 (BASELINE configs[2])",
+            "mnist_mlp": "MNISTClassifier 784-32-64-10 MLP, synthetic 28x28 (BASELINE configs[1])",
+            "bert_base": "BERT-base MLM seq 128 (BASELINE configs[3])"}.get(model, model)
+
+
 def _ref_batch(args, world):
     """Per-worker batch of the CPU arm: the GPU arm's 256 images when one worker has the whole host,
     256 // W with W workers, so that a step costs about the same host time at every N."""
@@ -240,6 +246,8 @@ def _parity_block(comm, rank, world, dev):
                 dist.all_reduce(ref)
                 mag = src.float().abs() / world
                 dist.all_reduce(mag)                       # sum_r |g_r| / W: the error denominator
+                exact = src.double() / world
+                dist.all_reduce(exact)                     # the mean in fp64: judges both arms in bf16
                 t = None
                 if comm.nvls_enabled:
                     try:
@@ -256,24 +264,39 @@ def _parity_block(comm, rank, world, dev):
                 comm.check_alive()
                 path = names[comm.stats()["last_algo"]]
                 got, want = t.float(), ref.float()
+                ibits = torch.int16 if dtype == torch.bfloat16 else torch.int32
                 fin = torch.isfinite(want) & torch.isfinite(got) & (mag < 3.0e38)
-                err = float(((got - want).abs()[fin] / mag[fin].clamp_min(1.1754944e-38)).max().item()) if bool(fin.any()) else 0.0
+                den = mag[fin].clamp_min(1.1754944e-38)
+
+                def worst(a, b):
+                    return float(((a - b).abs()[fin] / den).max().item()) if bool(fin.any()) else 0.0
+
+                err = worst(got, want)                                  # b2c against the reference path (NCCL)
+                err_exact = worst(got.double(), exact)                  # b2c against the fp64 mean
+                ref_err_exact = worst(want.double(), exact)             # NCCL against the fp64 mean
                 nan_ok = bool((torch.isnan(got) == torch.isnan(want)).all())
                 inf_ok = bool((got[torch.isinf(want)] == want[torch.isinf(want)]).all())
-                bit = bool(torch.equal(t.view(torch.int16 if dtype == torch.bfloat16 else torch.int32),
-                                       ref.view(torch.int16 if dtype == torch.bfloat16 else torch.int32)))
+                bit = bool(torch.equal(t.view(ibits), ref.view(ibits)))
                 rep = t.clone()
                 dist.broadcast(rep, src=0)
-                same = bool(torch.equal(rep.view(torch.int16 if dtype == torch.bfloat16 else torch.int32),
-                                        t.view(torch.int16 if dtype == torch.bfloat16 else torch.int32)))
-                bar = 1e-6 if dtype == torch.float32 else 2.0 ** -7   # fp32: 1e-6 of sum|g|/W; bf16: one ulp (2^-8 rel, + rounding)
-                good = same and nan_ok and inf_ok and (bit if kind == "int" else err <= bar)
+                same = bool(torch.equal(rep.view(ibits), t.view(ibits)))
+                if kind == "int":
+                    num_ok = bit
+                elif dtype == torch.float32:
+                    num_ok = err <= 1e-6
+                else:
+                    # bf16: within one bf16 ulp (2^-7 of the magnitude) of the exact mean, and no less accurate than
+                    # the reference path beyond half an ulp.  NCCL's ring / tree kernels accumulate bf16 hop by hop at
+                    # small sizes, so b2c-vs-NCCL itself can exceed one ulp while b2c is the closer of the two.
+                    num_ok = err_exact <= 2.0 ** -7 and err_exact <= ref_err_exact + 2.0 ** -9
+                good = same and nan_ok and inf_ok and num_ok
                 flags = torch.tensor([0 if good else 1], device=dev)
                 dist.all_reduce(flags)
                 good = int(flags.item()) == 0
                 ok = ok and good
                 rows.append({"op": "allreduce", "dtype": tag, "bytes": S, "payload": kind, "path": path, "in_arena": arena,
-                             "max_rel_err": err, "bit_exact_vs_nccl": bit, "replicas_identical": same, "ok": good})
+                             "max_rel_err": err, "max_rel_err_vs_fp64_mean": err_exact, "nccl_max_rel_err_vs_fp64_mean": ref_err_exact,
+                             "bit_exact_vs_nccl": bit, "replicas_identical": same, "ok": good})
                 if arena:
                     comm.nvls_free(t)
                 else:
@@ -298,11 +321,16 @@ def _parity_block(comm, rank, world, dev):
     for r in rows:
         if r["op"] == "allreduce":
             k = f'{r["dtype"]}/{r["path"]}'
-            summary[k] = max(summary.get(k, 0.0), r["max_rel_err"] if r["payload"] != "int" else 0.0)
+            if r["payload"] in ("randn", "wide"):
+                e = summary.setdefault(k, {"vs_nccl": 0.0, "vs_fp64_mean": 0.0, "nccl_vs_fp64_mean": 0.0})
+                e["vs_nccl"] = max(e["vs_nccl"], r["max_rel_err"])
+                e["vs_fp64_mean"] = max(e["vs_fp64_mean"], r["max_rel_err_vs_fp64_mean"])
+                e["nccl_vs_fp64_mean"] = max(e["nccl_vs_fp64_mean"], r["nccl_max_rel_err_vs_fp64_mean"])
     return {"ok": ok, "checks": len(rows), "failed": [r for r in rows if not r["ok"]][:8],
             "paths": sorted({r["path"] for r in rows}), "max_rel_err_by_dtype_and_path": summary,
-            "bars": "int payloads bit-exact vs NCCL; fp32 <= 1e-6 of sum|g|/W; bf16 <= 1 ulp; NaN/inf classes equal; "
-                    "replicas bitwise identical; broadcast byte-equal vs NCCL for every root",
+            "bars": "int payloads bit-exact vs NCCL; fp32 <= 1e-6 of sum|g|/W vs NCCL; bf16 within one bf16 ulp (2^-7 of sum|g|/W) of "
+                    "the fp64 mean and no less accurate than NCCL's own result (+ half an ulp); NaN/inf classes equal; replicas "
+                    "bitwise identical; broadcast byte-equal vs NCCL for every root",
             "rows": [r for r in rows if r["bytes"] in (31500000, 102441032) and r.get("payload", "randn") == "randn"]}
 
 
@@ -494,7 +522,11 @@ def run_b2c(args):
         buckets.append(row)
 
     parity = _parity_block(comm, rank, world, dev) if (world > 1 and not stock and not args.no_parity) else None
-    allreduce = _allreduce_section(args, comm, rank, world, dev) if not stock else None
+    ar_sizes = None
+    if own:
+        # the buckets this reducer really launches (16-byte multiples) plus torch DDP's two largest for continuity
+        ar_sizes = sorted({b.nbytes for b in ddp.reducer.buckets if b.nbytes >= (1 << 20)} | {31500000, 29664000})
+    allreduce = _allreduce_section(args, comm, rank, world, dev, ar_sizes) if (not stock and not args.no_allreduce_section) else None
     cpu_baseline = _cpu_baseline(args) if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
 
     if rank == 0:
@@ -504,8 +536,8 @@ def run_b2c(args):
             "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32" if args.wire != "bf16" else "f32 grads on a bf16 wire",
             "data": "synthetic",
-            "config": {"workload": f"{args.model} synthetic 224x224, batch {batch}/GPU, SGD momentum, 25 MB gradient "
-                                   f"buckets via RayAccelerator(use_gpu=True) plugin methods (BASELINE configs[2]); "
+            "config": {"workload": f"{_workload_name(args.model)}, batch {batch}/GPU, {opt_name}, 25 MB gradient "
+                                   f"buckets via RayAccelerator(use_gpu=True) plugin methods; "
                                    f"the CPU reference arm (--impl reference) runs batch {_ref_batch(args, world)}/worker",
                        "global_batch": batch * world, "parallelism": f"dp{world}",
                        "l2": "inputs larger than L2 (activations of a 256-image batch >> 126 MB); no flush needed",
@@ -620,7 +652,7 @@ def run_hvd(args):
 RESNET50_BUCKETS = [12415000, 31500000, 29664000, 27021000, 1625000]  # bytes, launch order
 
 
-def _allreduce_section(args, comm, rank, world, dev):
+def _allreduce_section(args, comm, rank, world, dev, sizes=None):
     """The second half of BASELINE.json's metric: gradient-allreduce bus GB/s on the real bucket sizes.
     N>1: over NVLink, b2c vs stock NCCL in the same processes.  N=1: there is no link; the same kernels
     run as 8 virtual ranks on the one GPU (HBM-bound), reported against the measured HBM peak."""
@@ -629,6 +661,7 @@ def _allreduce_section(args, comm, rank, world, dev):
     from ray_lightning_accelerators_b200 import _lib
     from ray_lightning_accelerators_b200.comm import ALGO_AUTO, ALGO_TWOSHOT, LocalGroup
     iters = args.ar_iters
+    sizes = list(sizes or RESNET50_BUCKETS)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     out = []
     peaks, peak_kind = _peaks()
@@ -677,7 +710,7 @@ def _allreduce_section(args, comm, rank, world, dev):
         return float(t.item())
 
     if world > 1:
-        for S in RESNET50_BUCKETS:
+        for S in sizes:
             if comm.nvls_enabled:
                 try:
                     x = comm.nvls_empty(S // 4)   # lives in the multicast arena: in-switch reduction, in place
@@ -728,7 +761,7 @@ def _allreduce_section(args, comm, rank, world, dev):
                 "buckets": out}
     g = LocalGroup(8, device=dev.index or 0, arena_bytes=8 << 20)
     g.set_param(_lib.PARAM_TIMEOUT_MS, 3000)
-    for S in RESNET50_BUCKETS:
+    for S in sizes:
         ts = [torch.randn(S // 4, device=dev) for _ in range(8)]
         us = timed(lambda: g.allreduce(ts, algo=ALGO_TWOSHOT), lambda: None)
         alg = 2.0 * 8 * S  # every virtual rank reads S and writes S (zero-copy two-shot, in place)
@@ -774,6 +807,7 @@ def main():
                     help="fold optimizer.step() into the bucket launches (default with the own reducer)")
     ap.add_argument("--no-fused-opt", dest="fused_opt", action="store_false")
     ap.add_argument("--no-parity", action="store_true", help="skip the cross-GPU parity block (N > 1)")
+    ap.add_argument("--no-allreduce-section", action="store_true", help="skip the bucket-size allreduce sweep after the training legs")
     ap.add_argument("--no-bucket-timing", action="store_true", help="no per-bucket CUDA events in the hook (host-bound tiny models)")
     args = ap.parse_args()
     if args.impl == "reference":
