@@ -23,32 +23,55 @@ from ray_lightning_accelerators_b200.comm import ALGO_NVLS, ALGO_ONESHOT, ALGO_T
 
 
 class LinkCounters:
-    """(tx_bytes, rx_bytes) summed over all links of one GPU."""
+    """(tx_bytes, rx_bytes) summed over all links of one GPU, or None when the box exposes no link counters."""
 
     def __init__(self, index):
         self.index = index
-        self.h = None
+        self.mode, self.how, self.errors = None, "unavailable", []
         try:
             import pynvml
             pynvml.nvmlInit()
             self.nv = pynvml
             self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.read()
-            self.how = "NVML field values NVLINK_THROUGHPUT_DATA_TX/RX (KiB), all links"
         except Exception as e:  # noqa: BLE001
-            self.h = None
-            self.how = f"nvidia-smi nvlink -gt d (NVML unavailable: {type(e).__name__})"
+            self.nv = None
+            self.errors.append(f"nvml init: {type(e).__name__}: {e}")
+        for mode in ("nvml_sum", "nvml_links", "smi"):
+            try:
+                self.mode = mode
+                self.read()
+                self.how = {"nvml_sum": "NVML field values NVLINK_THROUGHPUT_DATA_TX/RX (KiB), scope = all links",
+                            "nvml_links": "NVML field values NVLINK_THROUGHPUT_DATA_TX/RX (KiB), summed over links 0..17",
+                            "smi": "nvidia-smi nvlink -gt d (KiB per link, summed)"}[mode]
+                return
+            except Exception as e:  # noqa: BLE001
+                self.errors.append(f"{mode}: {type(e).__name__}: {e}")
+        self.mode = None
+        self.how = "unavailable on this box: " + " | ".join(self.errors)
+
+    @staticmethod
+    def _val(v):
+        t = int(v.valueType)
+        return int({0: v.value.dVal, 1: v.value.uiVal, 2: v.value.ulVal, 3: v.value.ullVal, 4: v.value.sllVal}.get(t, v.value.ullVal))
 
     def read(self):
-        if self.h is not None:
+        if self.mode is None:
+            return None
+        if self.mode in ("nvml_sum", "nvml_links"):
+            if self.nv is None:
+                raise RuntimeError("no NVML")
             nv = self.nv
-            ids = [getattr(nv, "NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX", 138), getattr(nv, "NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX", 139)]
-            vals = nv.nvmlDeviceGetFieldValues(self.h, [(i, 0xFFFFFFFF) for i in ids])   # scope UINT_MAX = sum over links
+            ids = [nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX]
+            scopes = [0xFFFFFFFF] if self.mode == "nvml_sum" else list(range(18))
             out = []
-            for v in vals:
-                if v.nvmlReturn != 0:
-                    raise RuntimeError(f"NVML field {v.fieldId}: return {v.nvmlReturn}")
-                out.append(int(v.value.ullVal) * 1024)
+            for i in ids:
+                vals = nv.nvmlDeviceGetFieldValues(self.h, [(i, sc) for sc in scopes])
+                tot = 0
+                for v in vals:
+                    if v.nvmlReturn != 0:
+                        raise RuntimeError(f"field {v.fieldId} scope {v.scopeId}: nvmlReturn {v.nvmlReturn}")
+                    tot += self._val(v)
+                out.append(tot * 1024)
             return tuple(out)
         txt = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(self.index)], capture_output=True, text=True).stdout
         tx = rx = 0
@@ -58,6 +81,8 @@ class LinkCounters:
                 tx += int(line.split(":")[-1].split()[0])
             elif "Data Rx" in line:
                 rx += int(line.split(":")[-1].split()[0])
+        if tx == 0 and rx == 0:
+            raise RuntimeError("no counters in nvidia-smi output: " + txt[:120].replace("\n", " / "))
         return tx * 1024, rx * 1024
 
 
@@ -95,7 +120,8 @@ def main():
         c1 = ctr.read() if ctr else None
         us = a.elapsed_time(b) * 1e3 / N
         if rank == 0:
-            tx, rx = (c1[0] - c0[0]) / N, (c1[1] - c0[1]) / N
+            have = c0 is not None and c1 is not None
+            tx, rx = ((c1[0] - c0[0]) / N, (c1[1] - c0[1]) / N) if have else (float("nan"), float("nan"))
             row = {"kernel": name, "bytes": size, "world": world, "us_per_launch_back_to_back": us,
                    "nvlink_tx_bytes_per_launch": tx, "nvlink_rx_bytes_per_launch": rx,
                    "algorithmic_tx_bytes": algorithmic_tx, "algorithmic_rx_bytes": algorithmic_rx,

@@ -94,7 +94,7 @@ def worker(args):
 
 def run_trials(groups, steps, tag, outdir):
     procs, outs = [], []
-    start_at = time.time() + 45.0          # every trial finishes set-up and warm-up before the shared start line
+    start_at = time.time() + 30.0          # every trial finishes set-up and warm-up before the shared start line
     for gi, gpus in enumerate(groups):
         port = 29800 + 7 * gi + (100 if tag == "solo" else 0)
         out = os.path.join(outdir, f"_tune_{tag}_{gi}.json")
