@@ -475,32 +475,43 @@ def run_b2c(args):
 
     # ---- roofline of the dominant b2c kernel of the timed region (largest share of our device time)
     peaks, peak_kind = _peaks()
-    dom = max(per_bucket_us, key=lambda nb: per_bucket_us[nb]) if per_bucket_us else None
+    # One kernel carries every bucket, so "the dominant kernel's average launch" is the mean over ALL its launches of
+    # the timed region: achieved = sum of algorithmic bytes / sum of CUDA-event durations (the 4 KB bucket included).
     roofline = None
-    if dom is not None:
-        us = per_bucket_us[dom]
+    if per_bucket_us:
+        sizes_ = sorted(per_bucket_us)
+        n_l = len(sizes_)
+        us = sum(per_bucket_us[nb] for nb in sizes_) / n_l
+        dom = max(sizes_)
         if world == 1:
             # fused SGD+momentum step, local: read g, w, m and write w, m = 20 bytes per fp32 parameter
-            alg = 5.0 * dom
+            alg = sum(5.0 * nb for nb in sizes_) / n_l
             roofline = {"bound": "hbm", "kernel": grad_kernel, "achieved": alg / us / 1e3,
                         "peak": peaks["hbm_gbs"], "peak_kind": f"{peak_kind} HBM copy", "unit": "GB/s",
                         "frac": alg / us / 1e3 / peaks["hbm_gbs"], "traffic": None,
-                        "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom,
-                        "note": "in-step: the kernel shares the GPU with the tail of backward"}
+                        "bytes_per_launch": alg, "us_per_launch": us, "launches_per_step": n_l,
+                        "largest_bucket": {"bytes": dom, "us": per_bucket_us[dom],
+                                           "frac": 5.0 * dom / per_bucket_us[dom] / 1e3 / peaks["hbm_gbs"]},
+                        "note": "in-step: the kernel shares the GPU with the tail of backward; mean over all bucket launches of a step"}
         else:
-            alg = 2.0 * (world - 1) / world * dom  # NVLink bytes per GPU per direction (busbw numerator)
+            f = 2.0 * (world - 1) / world   # NVLink bytes per GPU per direction per bucket byte (busbw numerator)
+            alg = sum(f * nb for nb in sizes_) / n_l
             roofline = {"bound": "nvlink", "kernel": grad_kernel,
                         "achieved": alg / us / 1e3, "peak": NVLINK_NOMINAL_GBPS,
                         "peak_kind": "nominal NVLink 5 per direction (measured peer copy 770 GB/s)", "unit": "GB/s",
                         "frac": alg / us / 1e3 / NVLINK_NOMINAL_GBPS,
                         "frac_of_measured_copy": alg / us / 1e3 / NVLINK_MEASURED_COPY_GBPS, "traffic": None,
-                        "bytes_per_launch": alg, "us_per_launch": us, "bucket_bytes": dom,
-                        "note": "in-step event time: includes the wait for the slowest rank at the entry barrier "
-                                "(see grad_buckets[*].wait_for_peers_us) and for a free SM"}
-            if dom in phases and isinstance(phases[dom], tuple):
-                data_us = phases[dom][1]
+                        "bytes_per_launch": alg, "us_per_launch": us, "launches_per_step": n_l,
+                        "largest_bucket": {"bytes": dom, "us": per_bucket_us[dom],
+                                           "frac": f * dom / per_bucket_us[dom] / 1e3 / NVLINK_NOMINAL_GBPS},
+                        "note": "in-step CUDA-event time, mean over all bucket launches of a step: it includes the wait for the "
+                                "slowest rank at the entry barrier (grad_buckets[*].wait_for_peers_us) — rank skew, not kernel work"}
+            ph = [phases[nb] for nb in sizes_ if nb in phases and isinstance(phases[nb], tuple)]
+            if len(ph) == n_l:
+                data_us = sum(p_[1] for p_ in ph) / n_l
                 roofline["data_phase_us"] = data_us
                 roofline["frac_data_phase"] = alg / data_us / 1e3 / NVLINK_NOMINAL_GBPS if data_us > 0 else None
+                roofline["wait_for_peers_us"] = sum(p_[0] for p_ in ph) / n_l
     if roofline is not None:
         try:  # per-launch DRAM bytes of this kernel from the committed ncu capture
             with open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")) as f:
