@@ -83,7 +83,9 @@ enum {
                                      switch (root sends its bytes once); 0: every rank pulls from the root */
   B2C_PARAM_MC_ACQ_POLL = 18,     /* multicast flag barrier: 1 (default) spin with ld.acquire.sys, 0 spin relaxed
                                      and fence once at the end (a measurement knob) */
-  B2C_PARAM__COUNT = 19
+  B2C_PARAM_BCAST_INPLACE_MIN_BYTES = 19, /* multicast broadcast of a tensor inside the arena: in place (two barriers,
+                                     no copy) from this size up, through a staging slot (one barrier) below; default 1 MiB */
+  B2C_PARAM__COUNT = 20
 };
 
 /* error codes */

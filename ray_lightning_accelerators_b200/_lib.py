@@ -36,6 +36,7 @@ PARAM_NVLS_STAGE_BYTES = 15
 PARAM_NVLS_LEAN = 16
 PARAM_BCAST_MC = 17
 PARAM_MC_ACQ_POLL = 18
+PARAM_BCAST_INPLACE_MIN_BYTES = 19
 PHASE_RING = 32
 REG_BLOB_BYTES = 128
 NVLS_BLOB_BYTES = 64

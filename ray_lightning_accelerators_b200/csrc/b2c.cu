@@ -160,6 +160,7 @@ static void default_params(b2c_comm* c) {
   c->params[B2C_PARAM_NVLS_LEAN] = 1;
   c->params[B2C_PARAM_BCAST_MC] = 1;
   c->params[B2C_PARAM_MC_ACQ_POLL] = 1;
+  c->params[B2C_PARAM_BCAST_INPLACE_MIN_BYTES] = 1l << 20;
   c->params[B2C_PARAM_NVLS_STAGE_BYTES] = 32l << 20;
 }
 
@@ -777,7 +778,10 @@ static int broadcast_impl(b2c_comm* c, void* const* bufs, bool group, size_t byt
     Nvls* nv = c->nvls;
     char* p = (char*)bufs[c->rank];
     // in place: the tensor itself lives in the arena (same offset on every rank), whole vectors only
-    const bool inside = p >= (char*)nv->uc && p + bytes <= (char*)nv->uc + nv->bytes && (((uintptr_t)p & 15u) == 0) && bytes % 16 == 0;
+    // (in place needs an entry barrier on top of the exit barrier — the root writes straight into the peers' tensor — so
+    // below 1 MiB, where the barriers are the whole cost, the staged form with its single barrier is the faster one)
+    const bool inside = p >= (char*)nv->uc && p + bytes <= (char*)nv->uc + nv->bytes && (((uintptr_t)p & 15u) == 0) && bytes % 16 == 0 &&
+                        bytes >= (size_t)c->params[B2C_PARAM_BCAST_INPLACE_MIN_BYTES];
     if (!inside) {
       rc = nvls_stage_slots(c);
       if (rc) return rc;
@@ -1685,6 +1689,7 @@ extern "C" int b2c_set_param(b2c_comm* c, int key, long v) {
       break;
     case B2C_PARAM_ZEROCOPY_MIN_BYTES:
     case B2C_PARAM_NVLS_MIN_BYTES:
+    case B2C_PARAM_BCAST_INPLACE_MIN_BYTES:
     case B2C_PARAM_CROSSOVER_BYTES:
       if (v < 0) return fail(B2C_EINVAL, "b2c_set_param: crossover=%ld", v);
       break;

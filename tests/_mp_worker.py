@@ -183,6 +183,7 @@ def main():
             comm.nvls_free(t)
         comm.set_param(_lib.PARAM_THREADS_NVLS, 512)
         # broadcast through the switch: bit-exact vs NCCL for every root, staged and in place, NaN bits included
+        comm.set_param(_lib.PARAM_BCAST_INPLACE_MIN_BYTES, 0)   # small tensors in place too (default: staged below 1 MiB)
         for n in (1, 17, 212904, (5 << 20) + 3):
             for root in range(world):
                 src = torch.from_numpy(np.random.default_rng(100 * root + rank).integers(0, 256, n, dtype=np.uint8)).to(dev)
@@ -201,6 +202,7 @@ def main():
                     torch.cuda.synchronize()
                     assert torch.equal(a[:m], c_), ("mc broadcast in place", n, root)
                     comm.nvls_free(c_)
+        comm.set_param(_lib.PARAM_BCAST_INPLACE_MIN_BYTES, 1 << 20)
         # the arena allocator: frees coalesce, and the same call sequence gives the same offsets on every rank
         p1, p2, p3 = comm.nvls_empty(1000), comm.nvls_empty(70000), comm.nvls_empty(1000)
         off2 = p2.data_ptr() - comm._nvls_base

@@ -156,6 +156,7 @@ def main():
     comm.check_alive()
 
     # ---------------- broadcast
+    comm.set_param(_lib.PARAM_BCAST_INPLACE_MIN_BYTES, 0)   # "mc in place" rows really are in place at every size
     for S in [int(x) for x in args.bcast.split(",")]:
         g = torch.Generator(device=dev).manual_seed(7 + rank)
         src = torch.randint(0, 256, (S,), generator=g, device=dev, dtype=torch.uint8)
