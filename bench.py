@@ -519,6 +519,11 @@ def run_b2c(args):
             if cap:
                 roofline["traffic"] = cap["dram_bytes_read"] + cap["dram_bytes_write"]
                 roofline["traffic_note"] = cap.get("note")
+            elif world > 1:
+                roofline["traffic_note"] = ("null: the cross-GPU kernels cannot run under ncu on this pool (flag barriers with live peers; "
+                                            "multi-rank commands under ncu are ruled out) and the NVLink counters are NOT_SUPPORTED "
+                                            "(profiles/r2_nvlink_bytes_w8.json); DRAM traffic of the same kernel family on one GPU: "
+                                            "profiles/r2_ncu_fused_summary.md")
         except Exception:
             pass
     buckets = []
@@ -558,6 +563,7 @@ def run_b2c(args):
                     "ms_per_step": float(ms2.item()) / K, "last_loss": last},
             "gpu_launches": int(launches), "b2c_launches_timed": int(n_timed),
             "clocks": clocks, "roofline": roofline, "grad_buckets": buckets, "parity": parity, "allreduce": allreduce,
+            "crossover_table": getattr(comm, "tuning", None),
         }
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline

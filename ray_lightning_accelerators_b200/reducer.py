@@ -89,6 +89,7 @@ class B2cReducer:
         self.passes = 0
         for run in plan_buckets(self.params, bucket_cap_bytes, first_bucket_bytes):
             self._make_bucket(run)
+        self._check_symmetric()
         for p in self.params:
             self._handles.append(p.register_post_accumulate_grad_hook(self._on_grad))
 
@@ -117,6 +118,18 @@ class B2cReducer:
         if comm is not None and flat.is_cuda and not in_arena and self.world > 1:
             comm.register(flat)      # collective, once: zero-copy peer-to-peer from the first step on
         self.buckets.append(b)
+
+    def _check_symmetric(self):
+        """The in-switch kernels address a bucket by its OFFSET in the multicast arena: every rank must hold every
+        bucket at the same offset with the same size.  The allocator is deterministic, so this only fails when the
+        ranks issued different allocation sequences — then nothing may be reduced in place."""
+        comm = self.comm
+        if comm is None or self.world == 1 or not any(b.in_arena for b in self.buckets):
+            return
+        mine = [(b.flat.data_ptr() - comm._nvls_base if b.in_arena else -1, b.nbytes) for b in self.buckets]
+        everyone = comm._exchange(mine)
+        if any(o != everyone[0] for o in everyone):
+            raise RuntimeError(f"gradient buckets sit at different offsets of the multicast arena on different ranks: {everyone}")
 
     @property
     def stream(self):
