@@ -255,11 +255,12 @@ class Comm(_Base):
             self._nvls_base, self._nvls_bytes, self._nvls_top = base.value, nbytes.value, 0
         return self._nvls
 
-    def autotune(self, sizes=(32 << 10, 128 << 10, 512 << 10, 2 << 20), iters=7, force=False):
+    def autotune(self, sizes=(32 << 10, 128 << 10, 512 << 10, 2 << 20, 8 << 20), iters=5, force=False):
         """Collective, once per comm: measure where each allreduce path starts to win at THIS world size on THIS
         box and set the AUTO thresholds from it (the crossover is measured, not assumed).
         Paths timed per size (fp32, CUDA events, median, max over ranks): staged one-shot, zero-copy two-shot on
-        a registered buffer, in-switch (NVLS) in place when the multicast arena is up.  Rank 0's table decides
+        a registered buffer, in-switch (NVLS) in place when the multicast arena is up (device time of back-to-back
+        calls; the host's launch path is kept out of the measurement).  Rank 0's table decides
         for everyone (thresholds must be identical on all ranks).  B2C_AUTOTUNE=0 keeps the built-in defaults;
         explicit B2C_* threshold variables still win afterwards.  Returns the table (also kept in .tuning)."""
         if self.world == 1 or (getattr(self, "tuning", None) is not None and not force):
@@ -290,14 +291,19 @@ class Comm(_Base):
                     for _ in range(3):
                         self.allreduce(t, scale=1.0 / self.world, algo=algo)
                     ts = []
+                    reps = 4
                     for _ in range(iters):
+                        # device time only: the GPU is kept busy while the host enqueues, and `reps` calls run back
+                        # to back between the two events (a single call after a sync would time the host's launch path)
                         self.barrier()
+                        torch.cuda._sleep(300000)
                         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                         a.record()
-                        self.allreduce(t, scale=1.0 / self.world, algo=algo)
+                        for _ in range(reps):
+                            self.allreduce(t, scale=1.0 / self.world, algo=algo)
                         b.record()
                         b.synchronize()
-                        ts.append(a.elapsed_time(b) * 1e3)
+                        ts.append(a.elapsed_time(b) * 1e3 / reps)
                     ts.sort()
                     row[name] = ts[len(ts) // 2]
                 if y is not None:
