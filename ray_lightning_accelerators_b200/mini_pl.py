@@ -235,6 +235,7 @@ class Trainer:
         `module` the LightningModule.  backward_fn / step_fn let the Horovod path synchronise."""
         module.trainer = self
         self.model = wrapped
+        self.optimizers = optimizers
         src = self.datamodule if self.datamodule is not None else module
         if self.datamodule is not None:
             self.datamodule.setup("fit")

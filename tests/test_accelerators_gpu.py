@@ -52,6 +52,29 @@ def test_ray_accelerator_two_gpus_train_and_device_contract(tmp_path):
     assert ray.live_actor_count() == 0
 
 
+def test_ray_accelerator_two_gpus_with_fused_optimizer(tmp_path, monkeypatch):
+    """B2C_FUSED_OPT=1: optimizer.step() is folded into the bucket launches on every worker (fused.FusedOptimizer);
+    the reference's train contract (weights change, come back to the driver, checkpoint loads) still holds and
+    the replicas end up bit-identical."""
+    _need(2)
+    monkeypatch.setenv("B2C_FUSED_OPT", "1")   # actors inherit the driver's environment
+
+    class Check(Callback):
+        def on_epoch_end(self, trainer, pl_module):
+            assert type(trainer.optimizers[0]).__name__ == "FusedOptimizer"
+            comm = trainer.accelerator_backend.b2c_comm
+            assert comm.stats()["fused_steps"] > 0
+            comm.check_alive()
+            import torch.distributed as dist
+            flat = torch.cat([p.detach().reshape(-1) for p in pl_module.parameters()])
+            ref = flat.clone()
+            dist.broadcast(ref, src=0)
+            assert torch.equal(ref, flat), "replicas differ after fused steps"
+
+    trainer = get_trainer(tmp_path, RayAccelerator(num_workers=2, use_gpu=True), use_gpu=True, callbacks=[Check()])
+    train_test(trainer, BoringModel())
+
+
 def test_horovod_accelerator_two_gpus(tmp_path):
     _need(2)
     trainer = get_trainer(tmp_path, HorovodRayAccelerator(num_hosts=1, num_slots=2, use_gpu=True), use_gpu=True)
