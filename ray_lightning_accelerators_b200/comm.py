@@ -258,7 +258,8 @@ class Comm(_Base):
     def autotune(self, sizes=(32 << 10, 128 << 10, 512 << 10, 2 << 20, 8 << 20), iters=5, force=False):
         """Collective, once per comm: measure where each allreduce path starts to win at THIS world size on THIS
         box and set the AUTO thresholds from it (the crossover is measured, not assumed).
-        Paths timed per size (fp32, CUDA events, median, max over ranks): staged one-shot, zero-copy two-shot on
+        Paths timed per size (fp32, CUDA events, median, max over ranks): the staged path AUTO would otherwise take
+        (one-shot up to the crossover, two-shot above; column "oneshot"), zero-copy two-shot on
         a registered buffer, in-switch (NVLS) in place when the multicast arena is up (device time of back-to-back
         calls; the host's launch path is kept out of the measurement).  Rank 0's table decides
         for everyone (thresholds must be identical on all ranks).  B2C_AUTOTUNE=0 keeps the built-in defaults;
@@ -273,6 +274,7 @@ class Comm(_Base):
         with torch.cuda.device(dev):
             for S in sizes:
                 n = S // 4
+                plain = torch.ones(n, device=dev)          # never registered: AUTO stages it (one-shot / two-shot)
                 x = torch.ones(n, device=dev)
                 reg = self.register(x)
                 y = None
@@ -281,7 +283,7 @@ class Comm(_Base):
                         y = self.nvls_empty(n).fill_(1.0)
                     except MemoryError:
                         y = None
-                cands = [("oneshot", x, ALGO_ONESHOT)]
+                cands = [("oneshot", plain, ALGO_AUTO)]     # "oneshot" = the staged path AUTO falls back to at this size
                 if reg:
                     cands.append(("zerocopy", x, ALGO_TWOSHOT))
                 if y is not None:
