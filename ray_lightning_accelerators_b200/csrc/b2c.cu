@@ -1277,6 +1277,8 @@ static int fused_impl(b2c_comm* c, void* const* grads, void* const* params, bool
     if (((uintptr_t)grads[r] | (uintptr_t)params[r]) & (W == 1 ? 3u : 15u))
       return fail(B2C_EINVAL, "b2c_fused_step: buckets must be 16-byte aligned");
     if ((need1 && !st1[r]) || (need2 && !st2[r])) return fail(B2C_EINVAL, "b2c_fused_step: optimizer state buffer missing");
+    if (W > 1 && ((need1 && ((uintptr_t)st1[r] & 15u)) || (need2 && ((uintptr_t)st2[r] & 15u))))
+      return fail(B2C_EINVAL, "b2c_fused_step: optimizer state buffers must be 16-byte aligned");
   }
   if (W > 1 && count % 4) return fail(B2C_EINVAL, "b2c_fused_step: count=%zu must be a multiple of 4 (buckets are padded to 16 bytes)", count);
   if (bcast_bytes && (bcast_root < 0 || bcast_root >= W)) return fail(B2C_EINVAL, "b2c_fused_step: bcast_root=%d", bcast_root);
