@@ -251,8 +251,16 @@ class B2cDataParallel(torch.nn.Module):
         """Fold `optimizer`'s step into the bucket launches (fused.FusedOptimizer); returns the object to use in
         its place.  Falls back to the optimizer itself when it is of an unsupported kind."""
         from . import fused
-        if not fused.supported(optimizer):
+        if not fused.supported(optimizer) or self._c4_folded or self.reducer.launch_fn is not None:
             return optimizer
+        for b in self.reducer.buckets:   # checked BEFORE anything is re-pointed: the fused step is fp32, one param_group per bucket
+            groups = {id(g) for g in optimizer.param_groups for p in g["params"] if any(p is q for q in b.params)}
+            owned = sum(1 for q in b.params if any(q is p for g in optimizer.param_groups for p in g["params"]))
+            if b.flat.dtype != torch.float32 or len(groups) != 1 or owned != len(b.params):
+                import warnings
+                warnings.warn("b2c: fused optimizer step not applicable (needs fp32 buckets whose parameters all belong to "
+                              "one param_group of this optimizer); keeping optimizer.step()")
+                return optimizer
         return fused.FusedOptimizer(optimizer, self)
 
     def forward(self, *args, **kwargs):

@@ -79,3 +79,21 @@ def test_no_sync_accumulates_without_launching():
     m(torch.randn(3, 8)).sum().backward()
     assert len(calls) == len(red.buckets)
     assert not torch.equal(m[0].weight.grad, g)         # second pass accumulated on top of the first
+
+
+def test_fuse_optimizer_declines_when_a_bucket_spans_param_groups():
+    """The fused step takes one set of hyper-parameters per bucket: an optimizer whose param_groups cut through a
+    bucket keeps its own step() (with a warning) instead of failing."""
+    import warnings
+    from ray_lightning_accelerators_b200.ddp_hook import B2cDataParallel
+    m = _model()
+    w = B2cDataParallel.__new__(B2cDataParallel)       # host logic only: no communicator on the CPU box
+    torch.nn.Module.__init__(w)
+    w.module, w._c4_folded = m, False
+    w.reducer = B2cReducer(m.parameters(), None, world=1)
+    opt = torch.optim.SGD([{"params": m[0].parameters()}, {"params": list(m[2].parameters()) + list(m[4].parameters()), "lr": 0.01}], lr=0.1)
+    with warnings.catch_warnings(record=True) as rec:
+        warnings.simplefilter("always")
+        assert w.fuse_optimizer(opt) is opt
+    assert any("not applicable" in str(r.message) for r in rec)
+    assert w.fuse_optimizer(torch.optim.RMSprop(m.parameters())) is not None   # unsupported kind: returned unchanged
