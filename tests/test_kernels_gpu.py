@@ -415,3 +415,38 @@ def test_error_paths_do_not_throw():
     with pytest.raises(_lib.B2cError):
         g.set_param(_lib.PARAM_THREADS, 100)
     g.close()
+
+
+def test_single_rank_average_is_a_no_op_without_a_launch():
+    """world = 1, scale = 1: the average over one rank is the input bit for bit (NaN payloads included), so the call
+    returns without launching anything; a custom scale still runs the streaming scale pass."""
+    from ray_lightning_accelerators_b200.comm import Comm
+    comm = Comm(0, 1, device=0, arena_bytes=1 << 20)
+    x = torch.from_numpy(O.payload("special", 4099, 0)).to(DEV)
+    before = x.clone()
+    l0 = comm.stats()["launches"]
+    comm.allreduce(x)
+    torch.cuda.synchronize()
+    st = comm.stats()
+    assert st["launches"] == l0 and st["noop_calls"] == 1
+    assert torch.equal(x.view(torch.int32), before.view(torch.int32))
+    y = torch.full((4099,), 3.0, device=DEV)
+    comm.allreduce(y, scale=0.5)
+    torch.cuda.synchronize()
+    assert comm.stats()["launches"] == l0 + 1 and bool((y == 1.5).all())
+    comm.close()
+
+
+def test_phase_ring_keeps_the_last_kernels_in_launch_order(groups):
+    """b2c_get_phase_ring: four %globaltimer stamps per kernel for the last 32 kernels of a comm, oldest first —
+    what bench.py uses to split the in-step time of a bucket into 'waiting for peers' and 'moving data'."""
+    g = groups(4)
+    ts = [torch.ones(50000, device=DEV) for _ in range(4)]
+    base = g.phase_ring_us()[1]
+    for _ in range(40):
+        g.allreduce(ts, algo=ALGO_TWOSHOT)
+    rows, total = g.phase_ring_us()
+    assert total == base + 40 and len(rows) == 32
+    starts = [r[3] for r in rows]
+    assert starts == sorted(starts) and len(set(starts)) == 32
+    assert all(r[0] >= 0 and r[1] >= 0 and r[0] + r[1] < 5000 for r in rows)   # microseconds, sane
